@@ -1,0 +1,65 @@
+"""ctypes binding of libdexgg.so (include/dexgg.h).  This is the binding INTEGRATION.md describes.
+
+The product path has no fallback: if the library is missing or the device is not a B200 every call raises.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libdexgg.so")
+
+_lib = None
+
+c_void_p, c_int, c_int64, c_size_t, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t, ctypes.c_float
+
+# name -> (restype, argtypes); every symbol include/dexgg.h declares
+SIGNATURES = {
+    "dexgg_version": (c_int, []),
+    "dexgg_last_error": (ctypes.c_char_p, []),
+    "dexgg_device_check": (c_int, []),
+    "dexgg_bps_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "dexgg_bps_encode": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int,
+                                 c_void_p, c_size_t, c_void_p]),
+    "dexgg_bps_encode_host": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int]),
+    "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
+}
+
+
+class DexggError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libdexgg error {code}: {msg}")
+        self.code = code
+
+
+def lib():
+    """Loads libdexgg.so (never builds it, never falls back)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run `python -m dex_gan_grasp_b200.build` (there is no CPU fallback)")
+        l = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise DexggError(rc, lib().dexgg_last_error().decode("utf-8", "replace"))
+
+
+def ptr(t):
+    """Device (or host) address of a torch tensor / numpy array / None."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        return t.data_ptr()
+    return t.ctypes.data
+
+
+def stream_ptr(device=None):
+    import torch
+    return torch.cuda.current_stream(device).cuda_stream

@@ -1,0 +1,444 @@
+// Stage 1 — Basis Point Set encoding on sm_100a.
+//
+// For every basis point b (P = 4096 in the reference) and every cloud: idx = argmin_k d2(x_k, b) with
+//   d2 = fma(dz,dz, fma(dy,dy, dx*dx))  (fp32, direct differences, lowest index wins an exact tie)
+// and dist = sqrt((dx^2 + dz^2) + dy^2) of the winner, the summation order that reproduces the reference's stored
+// encodings bit-exactly (oracle/bps_oracle.c; reference call sites DexGanGrasp/data/bps_encoder.py:28-55).
+//
+// Kernel design (bps_nn_packed_kernel):
+//   * one CTA = 128 threads x R basis points per thread, held in registers as packed f32x2 pairs;
+//   * the cloud is streamed through shared memory in tiles of 1024 points by 1-D TMA bulk copies
+//     (cp.async.bulk + mbarrier, double buffered) exactly as it lies in HBM (AoS, 12 B / point); three LDS.128
+//     broadcast four points to the whole CTA;
+//   * per (basis pair x point): FADD2 x3, FMUL2, FFMA2 x2 — the same six IEEE roundings per lane as the scalar
+//     form, at half the issue slots — and the running minimum is kept with one FMNMX3 per two points (ALU pipe);
+//   * the arg-min is recovered exactly: per 32-point chunk the CTA records which chunk first lowered the minimum
+//     (strict <), and at the end one warp re-evaluates that chunk (lane = point), `ballot(d == best)` gives the
+//     lowest matching index;
+//   * clouds can be split over blockIdx.z; partial results merge through atomicMin on the 64-bit key
+//     (d2 bits << 32 | index), which orders by distance first and by index second (d2 >= 0, so the float bit
+//     pattern is monotonic) — the same tie rule.
+//   * bps_finish_kernel gathers the winner and writes dist / idx.
+// Roofline: FP32 pipe (6 lane-ops per pair); see DESIGN.md.
+#include "common.cuh"
+
+namespace dexgg {
+
+constexpr int BPS_THREADS = 128;
+constexpr int BPS_TILE = 1024;  // points per shared-memory stage
+constexpr int BPS_CHUNK = 32;   // points per arg-min chunk (= one warp in the rescan)
+constexpr int BPS_STAGE_FLOATS = 3 * (BPS_TILE + BPS_CHUNK);
+#define BPS_SENTINEL 3.0e38f  // masked point: every distance to it is +inf
+
+__device__ __forceinline__ float search_d2(float bx, float by, float bz, float x, float y, float z) {
+    const float dx = __fsub_rn(x, bx), dy = __fsub_rn(y, by), dz = __fsub_rn(z, bz);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
+
+__device__ __forceinline__ f32x2 search_d2x2(f32x2 bx, f32x2 by, f32x2 bz, float x, float y, float z) {
+    const f32x2 dx = sub2(pack2(x, x), bx), dy = sub2(pack2(y, y), by), dz = sub2(pack2(z, z), bz);
+    return fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+}
+
+__device__ __forceinline__ unsigned long long make_key(float d2, uint32_t idx) {
+    return ((unsigned long long)__float_as_uint(d2) << 32) | idx;
+}
+
+template <int R>
+__global__ void __launch_bounds__(BPS_THREADS)
+bps_nn_packed_kernel(const float* __restrict__ basis, int P, const float* __restrict__ pts,
+                     const int64_t* __restrict__ offsets, int64_t uniform_n, int64_t total_points, int nsplit,
+                     unsigned long long* __restrict__ keys) {
+    static_assert(R % 2 == 0, "R must be even");
+    extern __shared__ __align__(128) unsigned char bps_smem[];
+    float* stage0 = reinterpret_cast<float*>(bps_smem);
+    float* stage1 = stage0 + BPS_STAGE_FLOATS;
+    float* s_best = stage1 + BPS_STAGE_FLOATS;                 // [R][BPS_THREADS]
+    int* s_chunk = reinterpret_cast<int*>(s_best + R * BPS_THREADS);  // [R][BPS_THREADS]
+    __shared__ uint64_t bar[2];
+
+    const int tid = threadIdx.x;
+    const int b = blockIdx.y;
+    const int64_t o0 = offsets ? offsets[b] : (int64_t)b * uniform_n;
+    const int64_t o1 = offsets ? offsets[b + 1] : o0 + uniform_n;
+    const int64_t n = o1 - o0;
+    const int64_t len = (((n + nsplit - 1) / nsplit) + 3) & ~(int64_t)3;
+    const int64_t r0 = o0 + (int64_t)blockIdx.z * len;
+    const int64_t r1 = (r0 + len < o1) ? r0 + len : o1;
+    if (r0 >= r1) return;  // uniform for the CTA
+    const int64_t g0 = r0 & ~(int64_t)3;  // local point 0 (48-byte aligned in HBM)
+    const int64_t span = r1 - g0;
+    const int ntiles = (int)((span + BPS_TILE - 1) / BPS_TILE);
+    const int64_t bulk_end = total_points & ~(int64_t)3;
+
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    auto issue = [&](int t) {  // tid 0 only
+        float* dst = (t & 1) ? stage1 : stage0;
+        const int64_t gs = g0 + (int64_t)t * BPS_TILE;
+        int64_t cnt = span - (int64_t)t * BPS_TILE;
+        if (cnt > BPS_TILE) cnt = BPS_TILE;
+        int64_t ge4 = gs + ((cnt + 3) & ~(int64_t)3);
+        if (ge4 > bulk_end) ge4 = bulk_end;
+        if (ge4 > gs) {
+            const uint32_t bytes = (uint32_t)((ge4 - gs) * 12);
+            fence_proxy_async();
+            mbar_expect_tx(&bar[t & 1], bytes);
+            bulk_g2s(dst, pts + 3 * gs, bytes, &bar[t & 1]);
+        } else {
+            mbar_arrive(&bar[t & 1]);
+        }
+    };
+    if (tid == 0) issue(0);
+
+    // basis points of this thread: p(r) = blockIdx.x * (THREADS*R) + r*THREADS + tid, pairs (2j, 2j+1)
+    const int pbase = blockIdx.x * (BPS_THREADS * R) + tid;
+    f32x2 bx[R / 2], by[R / 2], bz[R / 2];
+#pragma unroll
+    for (int j = 0; j < R / 2; ++j) {
+        float c[2][3];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int p = pbase + (2 * j + h) * BPS_THREADS;
+            const bool ok = p < P;
+            c[h][0] = ok ? basis[3 * p] : 0.f;
+            c[h][1] = ok ? basis[3 * p + 1] : 0.f;
+            c[h][2] = ok ? basis[3 * p + 2] : 0.f;
+        }
+        bx[j] = pack2(c[0][0], c[1][0]);
+        by[j] = pack2(c[0][1], c[1][1]);
+        bz[j] = pack2(c[0][2], c[1][2]);
+    }
+    float best[R];
+    int bchunk[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        best[r] = __int_as_float(0x7f800000);
+        bchunk[r] = -1;
+    }
+
+    for (int t = 0; t < ntiles; ++t) {
+        if (tid == 0 && t + 1 < ntiles) issue(t + 1);
+        float* st = (t & 1) ? stage1 : stage0;
+        mbar_wait(&bar[t & 1], (t >> 1) & 1);
+        // ---- fix-up: mask points outside [r0, r1), plain-load the <= 3 points past the last 48-byte group ----
+        const int64_t gs = g0 + (int64_t)t * BPS_TILE;
+        int cnt = (int)((span - (int64_t)t * BPS_TILE) < BPS_TILE ? (span - (int64_t)t * BPS_TILE) : BPS_TILE);
+        const int npad = (cnt + BPS_CHUNK - 1) & ~(BPS_CHUNK - 1);
+        const int lo_valid = (t == 0) ? (int)(r0 - g0) : 0;
+        int bulk_local_end = (int)((bulk_end - gs) < 0 ? 0 : ((bulk_end - gs) > cnt ? cnt : (bulk_end - gs)));
+        for (int j = tid; j < lo_valid; j += BPS_THREADS) {
+            st[3 * j] = BPS_SENTINEL;
+            st[3 * j + 1] = BPS_SENTINEL;
+            st[3 * j + 2] = BPS_SENTINEL;
+        }
+        for (int j = bulk_local_end + tid; j < npad; j += BPS_THREADS) {
+            float x = BPS_SENTINEL, y = BPS_SENTINEL, z = BPS_SENTINEL;
+            if (j < cnt) {
+                const float* g = pts + 3 * (gs + j);
+                x = g[0];
+                y = g[1];
+                z = g[2];
+            }
+            st[3 * j] = x;
+            st[3 * j + 1] = y;
+            st[3 * j + 2] = z;
+        }
+        __syncthreads();
+
+        const float4* s4 = reinterpret_cast<const float4*>(st);
+        const int nchunks = npad / BPS_CHUNK;
+        for (int c = 0; c < nchunks; ++c) {
+            float cur[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) cur[r] = best[r];
+#pragma unroll 2
+            for (int q = 0; q < BPS_CHUNK / 4; ++q) {
+                const float4 v0 = s4[(c * (BPS_CHUNK / 4) + q) * 3 + 0];
+                const float4 v1 = s4[(c * (BPS_CHUNK / 4) + q) * 3 + 1];
+                const float4 v2 = s4[(c * (BPS_CHUNK / 4) + q) * 3 + 2];
+#pragma unroll
+                for (int j = 0; j < R / 2; ++j) {
+                    const f32x2 da = search_d2x2(bx[j], by[j], bz[j], v0.x, v0.y, v0.z);
+                    const f32x2 db = search_d2x2(bx[j], by[j], bz[j], v0.w, v1.x, v1.y);
+                    const f32x2 dc = search_d2x2(bx[j], by[j], bz[j], v1.z, v1.w, v2.x);
+                    const f32x2 dd = search_d2x2(bx[j], by[j], bz[j], v2.y, v2.z, v2.w);
+                    float a0, a1, b0, b1, c0, c1, d0, d1;
+                    unpack2(da, a0, a1);
+                    unpack2(db, b0, b1);
+                    unpack2(dc, c0, c1);
+                    unpack2(dd, d0, d1);
+                    cur[2 * j] = min3(min3(cur[2 * j], a0, b0), c0, d0);
+                    cur[2 * j + 1] = min3(min3(cur[2 * j + 1], a1, b1), c1, d1);
+                }
+            }
+            const int gc = t * (BPS_TILE / BPS_CHUNK) + c;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (cur[r] < best[r]) {
+                    best[r] = cur[r];
+                    bchunk[r] = gc;
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- exact arg-min: one warp per basis point re-evaluates the winning 32-point chunk ----
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        s_best[r * BPS_THREADS + tid] = best[r];
+        s_chunk[r * BPS_THREADS + tid] = bchunk[r];
+    }
+    __syncthreads();
+    const int lane = tid & 31, warp = tid >> 5;
+    const int pblock = blockIdx.x * (BPS_THREADS * R);
+    for (int e = warp; e < BPS_THREADS * R; e += BPS_THREADS / 32) {
+        const int p = pblock + e;  // e = r*THREADS + t  <->  p(r) of thread t
+        if (p >= P) break;
+        const int ch = s_chunk[e];
+        if (ch < 0) continue;  // no finite distance in this range
+        const float bd = s_best[e];
+        const float qx = basis[3 * p], qy = basis[3 * p + 1], qz = basis[3 * p + 2];
+        const int64_t g = g0 + (int64_t)ch * BPS_CHUNK + lane;
+        float d = __int_as_float(0x7f800000);
+        if (g >= r0 && g < r1) {
+            const float* gp = pts + 3 * g;
+            d = search_d2(qx, qy, qz, gp[0], gp[1], gp[2]);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, d == bd);
+        if (lane == 0 && m != 0) {
+            const int64_t gi = g0 + (int64_t)ch * BPS_CHUNK + (__ffs(m) - 1);
+            atomicMin(&keys[(size_t)b * P + p], make_key(bd, (uint32_t)(gi - o0)));
+        }
+    }
+}
+
+// Simple scalar compare-select form: one thread per (cloud, basis point); cross-check of the packed kernel.
+__global__ void __launch_bounds__(128)
+bps_nn_scalar_kernel(const float* __restrict__ basis, int P, const float* __restrict__ pts,
+                     const int64_t* __restrict__ offsets, int64_t uniform_n, unsigned long long* __restrict__ keys) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
+    if (p >= P) return;
+    const int64_t o0 = offsets ? offsets[b] : (int64_t)b * uniform_n;
+    const int64_t o1 = offsets ? offsets[b + 1] : o0 + uniform_n;
+    const float qx = basis[3 * p], qy = basis[3 * p + 1], qz = basis[3 * p + 2];
+    float best = __int_as_float(0x7f800000);
+    int64_t bi = -1;
+    for (int64_t k = o0; k < o1; ++k) {
+        const float d = search_d2(qx, qy, qz, pts[3 * k], pts[3 * k + 1], pts[3 * k + 2]);
+        if (bi < 0 || d < best) {
+            best = d;
+            bi = k;
+        }
+    }
+    if (bi >= 0) keys[(size_t)b * P + p] = make_key(best, (uint32_t)(bi - o0));
+}
+
+__global__ void bps_finish_kernel(const float* __restrict__ basis, int P, const float* __restrict__ pts,
+                                  const int64_t* __restrict__ offsets, int64_t uniform_n, int B,
+                                  const unsigned long long* __restrict__ keys, float* __restrict__ dists,
+                                  int32_t* __restrict__ idx_out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)B * P) return;
+    const int b = (int)(i / P), p = (int)(i % P);
+    const unsigned long long key = keys[i];
+    const uint32_t k = (uint32_t)(key & 0xffffffffu);
+    float dist = __int_as_float(0x7f800000);
+    int32_t id = -1;
+    if (key != ~0ull) {
+        const int64_t o0 = offsets ? offsets[b] : (int64_t)b * uniform_n;
+        const float* g = pts + 3 * (o0 + k);
+        const float dx = __fsub_rn(g[0], basis[3 * p]), dy = __fsub_rn(g[1], basis[3 * p + 1]),
+                    dz = __fsub_rn(g[2], basis[3 * p + 2]);
+        const float sx = __fmul_rn(dx, dx), sy = __fmul_rn(dy, dy), sz = __fmul_rn(dz, dz);
+        dist = __fsqrt_rn(__fadd_rn(__fadd_rn(sx, sz), sy));
+        id = (int32_t)k;
+    }
+    dists[i] = dist;
+    if (idx_out) idx_out[i] = id;
+}
+
+// ---- FP32-pipe probe (roofline denominator for the BPS kernel) ----
+template <int KIND>
+__global__ void __launch_bounds__(256) fp32_probe_kernel(int iters, float* out) {
+    float a[8], s = 1.0000001f + threadIdx.x * 1e-9f, t = 1e-7f;
+    f32x2 v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        a[i] = i * 0.5f + threadIdx.x;
+        v[i] = pack2(a[i], a[i] + 1.f);
+    }
+    const f32x2 s2 = pack2(s, s), t2 = pack2(t, t);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (KIND == 0) a[i] = __fmaf_rn(a[i], s, t);
+                if (KIND == 1) v[i] = fma2(v[i], s2, t2);
+                if (KIND == 2) v[i] = add2(v[i], t2);
+                if (KIND == 3) a[i] = min3(a[i], a[(i + 1) & 7] + 0.f, s);
+            }
+        }
+    }
+    float r = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float lo, hi;
+        unpack2(v[i], lo, hi);
+        r += a[i] + lo + hi;
+    }
+    if (r == 123.456f) out[0] = r;
+}
+
+}  // namespace dexgg
+
+using namespace dexgg;
+
+extern "C" size_t dexgg_bps_workspace_bytes(int B, int P) {
+    if (B < 0 || P < 0) return 0;
+    return align_up((size_t)B * (size_t)P * sizeof(unsigned long long), 256);
+}
+
+template <int R>
+static int launch_packed(const float* basis, int P, const float* pts, const int64_t* offsets, int B, int64_t uniform_n,
+                         int64_t total, int nsplit, unsigned long long* keys, cudaStream_t st) {
+    const size_t smem = 2 * BPS_STAGE_FLOATS * sizeof(float) + (size_t)R * BPS_THREADS * 8;
+    static bool attr_set = false;
+    if (!attr_set && smem > 48 * 1024) {
+        DEXGG_CUDA_OK(cudaFuncSetAttribute(bps_nn_packed_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    dim3 grid((P + BPS_THREADS * R - 1) / (BPS_THREADS * R), B, nsplit);
+    bps_nn_packed_kernel<R><<<grid, BPS_THREADS, smem, st>>>(basis, P, pts, offsets, uniform_n, total, nsplit, keys);
+    DEXGG_LAUNCH_OK("bps_nn_packed_kernel");
+    return DEXGG_OK;
+}
+
+extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
+                                int64_t max_cloud_points, int64_t total_points, float* dists, int32_t* idx, int flags,
+                                void* workspace, size_t workspace_bytes, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(P >= 1 && B >= 0 && max_cloud_points >= 0 && total_points >= 0, "bps_encode: bad sizes P=%d B=%d", P, B);
+    if (B == 0) return DEXGG_OK;
+    DEXGG_REQUIRE(basis && dists && (pts || total_points == 0), "bps_encode: null pointer");
+    DEXGG_REQUIRE(B <= 65535, "bps_encode: at most 65535 clouds per call (got %d)", B);
+    DEXGG_REQUIRE((reinterpret_cast<uintptr_t>(pts) & 15) == 0, "bps_encode: pts must be 16-byte aligned");
+    DEXGG_REQUIRE(max_cloud_points < (1ll << 32), "bps_encode: cloud too large");
+    if (!offsets) DEXGG_REQUIRE(total_points == (int64_t)B * max_cloud_points, "bps_encode: uniform clouds need total_points == B*max_cloud_points");
+    if (!workspace || workspace_bytes < dexgg_bps_workspace_bytes(B, P)) {
+        set_error("bps_encode: workspace of %zu bytes needed, %zu given", dexgg_bps_workspace_bytes(B, P), workspace_bytes);
+        return DEXGG_E_WORKSPACE;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned long long* keys = static_cast<unsigned long long*>(workspace);
+    DEXGG_CUDA_OK(cudaMemsetAsync(keys, 0xff, (size_t)B * P * sizeof(unsigned long long), st));
+    if (total_points > 0 && max_cloud_points > 0) {
+        if (flags & DEXGG_BPS_SCALAR) {
+            dim3 grid((P + 127) / 128, B);
+            bps_nn_scalar_kernel<<<grid, 128, 0, st>>>(basis, P, pts, offsets, max_cloud_points, keys);
+            DEXGG_LAUNCH_OK("bps_nn_scalar_kernel");
+        } else {
+            constexpr int R = 16;
+            const int gx = (P + BPS_THREADS * R - 1) / (BPS_THREADS * R);
+            int nsplit = (flags >> 8) & 0xff;
+            if (nsplit == 0) {
+                const int64_t want = 2ll * 4 * sm_count();  // two waves of 4 CTAs per SM
+                const int64_t have = (int64_t)gx * B;
+                int64_t s = (want + have - 1) / have;
+                const int64_t smax = (max_cloud_points + 2047) / 2048;  // keep >= ~2048 points per split
+                if (s > smax) s = smax;
+                if (s < 1) s = 1;
+                if (s > 255) s = 255;
+                nsplit = (int)s;
+            }
+            int rc = launch_packed<R>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st);
+            if (rc != DEXGG_OK) return rc;
+        }
+    }
+    const size_t tot = (size_t)B * P;
+    bps_finish_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(basis, P, pts, offsets, max_cloud_points, B, keys, dists, idx);
+    DEXGG_LAUNCH_OK("bps_finish_kernel");
+    return DEXGG_OK;
+}
+
+extern "C" int dexgg_bps_encode_host(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
+                                     float* dists, int32_t* idx, int flags) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(P >= 1 && B >= 0 && basis && offsets && dists, "bps_encode_host: bad arguments");
+    if (B == 0) return DEXGG_OK;
+    const int64_t total = offsets[B];
+    int64_t maxn = 0;
+    for (int b = 0; b < B; ++b) {
+        DEXGG_REQUIRE(offsets[b + 1] >= offsets[b], "bps_encode_host: offsets must be non-decreasing");
+        if (offsets[b + 1] - offsets[b] > maxn) maxn = offsets[b + 1] - offsets[b];
+    }
+    float *d_basis = nullptr, *d_pts = nullptr, *d_dists = nullptr;
+    int64_t* d_off = nullptr;
+    int32_t* d_idx = nullptr;
+    void* ws = nullptr;
+    const size_t wsb = dexgg_bps_workspace_bytes(B, P);
+    int rc = DEXGG_OK;
+    cudaError_t e;
+#define HOST_TRY(x)                                                          \
+    if (rc == DEXGG_OK && (e = (x)) != cudaSuccess) {                        \
+        set_error("%s failed: %s", #x, cudaGetErrorString(e));               \
+        rc = DEXGG_E_CUDA;                                                   \
+    }
+    HOST_TRY(cudaMalloc(&d_basis, (size_t)P * 12));
+    HOST_TRY(cudaMalloc(&d_pts, (size_t)(total > 0 ? total : 1) * 12 + 16));
+    HOST_TRY(cudaMalloc(&d_off, (size_t)(B + 1) * 8));
+    HOST_TRY(cudaMalloc(&d_dists, (size_t)B * P * 4));
+    HOST_TRY(cudaMalloc(&d_idx, (size_t)B * P * 4));
+    HOST_TRY(cudaMalloc(&ws, wsb));
+    HOST_TRY(cudaMemcpy(d_basis, basis, (size_t)P * 12, cudaMemcpyHostToDevice));
+    if (total > 0) HOST_TRY(cudaMemcpy(d_pts, pts, (size_t)total * 12, cudaMemcpyHostToDevice));
+    HOST_TRY(cudaMemcpy(d_off, offsets, (size_t)(B + 1) * 8, cudaMemcpyHostToDevice));
+    if (rc == DEXGG_OK)
+        rc = dexgg_bps_encode(d_basis, P, d_pts, d_off, B, maxn, total, d_dists, d_idx, flags, ws, wsb, nullptr);
+    HOST_TRY(cudaMemcpy(dists, d_dists, (size_t)B * P * 4, cudaMemcpyDeviceToHost));
+    if (idx) HOST_TRY(cudaMemcpy(idx, d_idx, (size_t)B * P * 4, cudaMemcpyDeviceToHost));
+#undef HOST_TRY
+    cudaFree(d_basis);
+    cudaFree(d_pts);
+    cudaFree(d_off);
+    cudaFree(d_dists);
+    cudaFree(d_idx);
+    cudaFree(ws);
+    return rc;
+}
+
+extern "C" int dexgg_fp32_pipe_probe(int kind, int iters, float* ms, double* lane_ops) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(kind >= 0 && kind <= 3 && iters > 0 && ms && lane_ops, "fp32_pipe_probe: bad arguments");
+    float* out = nullptr;
+    DEXGG_CUDA_OK(cudaMalloc(&out, 4));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int grid = sm_count() * 8, block = 256;
+    for (int rep = 0; rep < 2; ++rep) {  // first launch warms up
+        cudaEventRecord(e0);
+        if (kind == 0) fp32_probe_kernel<0><<<grid, block>>>(iters, out);
+        if (kind == 1) fp32_probe_kernel<1><<<grid, block>>>(iters, out);
+        if (kind == 2) fp32_probe_kernel<2><<<grid, block>>>(iters, out);
+        if (kind == 3) fp32_probe_kernel<3><<<grid, block>>>(iters, out);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+    }
+    cudaEventElapsedTime(ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    DEXGG_LAUNCH_OK("fp32_probe_kernel");
+    const double per_thread = (double)iters * 64.0 * ((kind == 1 || kind == 2) ? 2.0 : 1.0);
+    *lane_ops = per_thread * (double)grid * block;
+    return DEXGG_OK;
+}

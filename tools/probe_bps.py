@@ -1,0 +1,56 @@
+"""GPU probe: FP32-pipe peaks (FFMA / FFMA2 / FADD2 / FMNMX3) and BPS kernel timings. Writes gpurun_out/probe_bps.json."""
+import ctypes
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from dex_gan_grasp_b200 import _native, bps as bps_mod  # noqa: E402
+
+L = _native.lib()
+out = {"gpu": torch.cuda.get_device_name(0), "sms": torch.cuda.get_device_properties(0).multi_processor_count}
+names = {0: "ffma", 1: "ffma2", 2: "fadd2", 3: "fmnmx3"}
+for kind, nm in names.items():
+    ms = ctypes.c_float()
+    ops = ctypes.c_double()
+    _native.check(L.dexgg_fp32_pipe_probe(kind, 4000, ctypes.byref(ms), ctypes.byref(ops)))
+    out["probe_" + nm] = {"ms": ms.value, "lane_ops_per_s": ops.value / (ms.value * 1e-3)}
+    print(nm, ms.value, "ms", ops.value / (ms.value * 1e-3) / 1e12, "T lane-ops/s", flush=True)
+
+basis = torch.from_numpy(np.load(bps_mod.BASIS_PATH)).cuda()
+
+
+def timeit(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ts = []
+    for _ in range(iters):
+        e0.record()
+        fn()
+        e1.record()
+        e1.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.median(ts)), float(np.min(ts))
+
+
+ws = bps_mod._Workspace()
+res = []
+for (B, N) in [(1024, 2048), (1, 16384), (1, 100000), (64, 16384), (4096, 1024), (8, 100000)]:
+    pts = 0.08 * torch.randn((B, N, 3), device="cuda")
+    for name, flags in [("packed", 0), ("packed_ns1", 1 << 8), ("packed_ns2", 2 << 8), ("packed_ns4", 4 << 8), ("scalar", 1)]:
+        if name == "scalar" and B * N > 3e6:
+            continue
+        med, mn = timeit(lambda: bps_mod.bps_encode_device(basis, pts, flags=flags, ws=ws))
+        pairs = 4096.0 * B * N
+        r = {"B": B, "N": N, "variant": name, "ms_median": med, "ms_min": mn, "gpairs_per_s": pairs / (med * 1e-3) / 1e9,
+             "fp32_lane_ops_per_s": 6 * pairs / (med * 1e-3)}
+        res.append(r)
+        print(r, flush=True)
+out["bps"] = res
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(out, open("gpurun_out/probe_bps.json", "w"), indent=1)
