@@ -21,6 +21,21 @@ SIGNATURES = {
     "dexgg_bps_encode": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int,
                                  c_void_p, c_size_t, c_void_p]),
     "dexgg_bps_encode_host": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int]),
+    "dexgg_net_create": (c_int, [c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, ctypes.POINTER(c_void_p)]),
+    "dexgg_net_update": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "dexgg_net_destroy": (None, [c_void_p]),
+    "dexgg_net_workspace_bytes": (c_size_t, [c_void_p, c_int64, c_int64]),
+    "dexgg_generator_forward": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_float, c_void_p, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "dexgg_evaluator_forward": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
+                                        c_size_t, c_void_p]),
+    "dexgg_discriminator_forward": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
+                                            c_void_p, c_void_p, c_size_t, c_void_p]),
+    "dexgg_filter_topk": (c_int, [c_void_p, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dexgg_linear_f32": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                 c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "dexgg_rot6d_forward": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "dexgg_rot6d_backward": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
 }
 

@@ -1,0 +1,55 @@
+// Fused linear layer  C = epilogue(A · Wᵀ)  shared by the fp32 CUDA-core kernel (linear_simt.cu) and the bf16
+// tcgen05 kernel (linear_umma.cu).  The epilogue is what turns a GEMM into a layer of the reference's ResBlock
+// (DexGanGrasp/models/networks.py:43-56):
+//     v = acc
+//     v += base[((row0 + m) / rows_per_obj) * ldbase + n]     per-object hoisted BPS projection (SURVEY §8a note H)
+//     v += bias[n]
+//     v  = v * scale[n] + shift[n]                    BatchNorm (eval) folded to an affine
+//     v += residual[m * ldr + n]                      ResBlock skip branch
+//     v  = act ? leaky_relu(v, 0.2) : v
+//     C[m * ldc + n] = v (+ beta * C)
+#pragma once
+#include "common.cuh"
+
+namespace dexgg {
+
+struct Epilogue {
+    const float* base = nullptr;
+    int64_t ldbase = 0;
+    int rows_per_obj = 1;
+    int64_t row0 = 0;  // global row index of row 0 of this call (chunked calls): object = (row0 + m) / rows_per_obj
+    const float* bias = nullptr;
+    const float* scale = nullptr;
+    const float* shift = nullptr;
+    const float* residual = nullptr;
+    int64_t ldr = 0;
+    int act = 0;         // 1 = LeakyReLU(0.2)
+    int accumulate = 0;  // 1: C += v (used by weight gradients)
+};
+
+struct LinearF32 {
+    const float* A = nullptr;  // [M,K]: A[m*lda + k]   (trans_a: A[k*lda + m])
+    int64_t lda = 0;
+    const float* W = nullptr;  // [N,K]: W[n*ldw + k]   (trans_w: W[k*ldw + n])
+    int64_t ldw = 0;
+    int M = 0, N = 0, K = 0;
+    int trans_a = 0, trans_w = 0;
+    float* C = nullptr;
+    int64_t ldc = 0;
+    Epilogue ep;
+};
+
+int linear_f32(const LinearF32& p, cudaStream_t st);  // linear_simt.cu
+
+#define DEXGG_LRELU_SLOPE 0.2f
+
+__device__ __forceinline__ float apply_epilogue(const Epilogue& ep, float v, int m, int n) {
+    if (ep.base) v += ep.base[((ep.row0 + m) / ep.rows_per_obj) * ep.ldbase + n];
+    if (ep.bias) v += ep.bias[n];
+    if (ep.scale) v = fmaf(v, ep.scale[n], ep.shift[n]);
+    if (ep.residual) v += ep.residual[(int64_t)m * ep.ldr + n];
+    if (ep.act) v = v > 0.f ? v : DEXGG_LRELU_SLOPE * v;
+    return v;
+}
+
+}  // namespace dexgg

@@ -1,0 +1,453 @@
+// Stages 2-3 — DexGenerator, Discriminator and DexEvaluator forwards (eval-mode BatchNorm) as chains of fused linear
+// layers, with the per-object hoisting of the shared BPS projection (SURVEY.md §8a note H).
+//
+// Reference: DexGanGrasp/models/networks.py — ResBlock :26-56, Generator.forward :88-103, Discriminator.forward
+// :148-159, DexEvaluator.forward :315-337; utils.rot_matrix_from_ortho6d (utils/utils.py:380-394) and
+// utils.translate_along_axis (utils/utils.py:19-48) in the generator epilogue.
+//
+// A net handle owns PACKED weights derived from the caller's fp32 parameters:
+//   Wb  [768*n_blocks, 4096]  the BPS columns of every block's fc1 (256 rows) and fc3 (512 rows), input BatchNorm folded
+//   bb  [768*n_blocks]        their biases plus the folded BatchNorm shift
+//   per block: Wt [768, KT]   the remaining columns in the order [previous X (512) | tail | zero pad], KT = 512+tailw or tailw
+//              sc/sh [768]    bn1 affine for the fc1 rows, identity for the fc3 rows
+//              W2 [512,256], sc2/sh2 [512]   fc2 with bn2 (and fc2's bias) folded into the affine
+//   heads Wh [nh,512], bh [nh]
+// "tail" = the per-row inputs that are not BPS: z (generator), bn1(rot9,transl3) (evaluator), bn1(rot9,transl3,joints)
+// (discriminator), zero-padded to tailw = 16 or 32 columns.
+#include "linear.cuh"
+
+#include <new>
+
+namespace dexgg {
+
+constexpr int IN_BPS = 4096, HID = 512, INNER = 256, NCAT = INNER + HID;  // 768 = fc1 ‖ fc3
+constexpr float BN_EPS = 1e-5f;
+constexpr int64_t CHUNK_ROWS = 32768;
+
+// ---------------------------------------------------------------- packing kernels
+__global__ void bn_affine_kernel(const float* w, const float* b, const float* rm, const float* rv, int n, float* a, float* c) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const float s = w[i] / sqrtf(rv[i] + BN_EPS);
+        a[i] = s;
+        c[i] = b[i] - s * rm[i];
+    }
+}
+// dst[r, dcol0 + j] = src[r, scol0 + j] * (colscale ? colscale[j] : 1)
+__global__ void pack_cols_kernel(float* dst, int64_t ldd, int dcol0, const float* src, int64_t lds, int scol0, int ncols,
+                                 int nrows, const float* colscale) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)ncols * nrows) return;
+    const int r = (int)(i / ncols), j = (int)(i % ncols);
+    dst[r * ldd + dcol0 + j] = src[r * lds + scol0 + j] * (colscale ? colscale[j] : 1.f);
+}
+// dst[r] = bias[r] + sum_j src[r, scol0 + j] * c[j]      (one warp per row)
+__global__ void fold_bias_kernel(float* dst, const float* bias, const float* src, int64_t lds, int scol0, int ncols,
+                                 int nrows, const float* c) {
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (r >= nrows) return;
+    float s = 0.f;
+    if (c)
+        for (int j = lane; j < ncols; j += 32) s = fmaf(src[r * lds + scol0 + j], c[j], s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) dst[r] = bias[r] + s;
+}
+__global__ void fill_kernel(float* p, float v, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+// sc2 = a; sh2 = a * bias + c
+__global__ void affine_bias_kernel(const float* a, const float* c, const float* bias, int n, float* sc, float* sh) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        sc[i] = a[i];
+        sh[i] = fmaf(a[i], bias[i], c[i]);
+    }
+}
+
+// ---------------------------------------------------------------- per-row helper kernels
+// Concatenate up to three per-row sources, apply the input-BatchNorm affine, zero-pad to `width` and write the tail
+// columns of up to three activation buffers.
+struct TailDst {
+    float* p[3];
+    int64_t ld[3];
+};
+__global__ void pack_tail_kernel(const float* s0, int n0, const float* s1, int n1, const float* s2, int n2, const float* a,
+                                 const float* c, int width, int64_t M, TailDst d) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M * width) return;
+    const int64_t m = i / width;
+    const int j = (int)(i % width);
+    float v = 0.f;
+    if (j < n0) v = s0[m * n0 + j];
+    else if (j < n0 + n1) v = s1[m * n1 + (j - n0)];
+    else if (j < n0 + n1 + n2) v = s2[m * n2 + (j - n0 - n1)];
+    if (a && j < n0 + n1 + n2) v = fmaf(a[j], v, c[j]);
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        if (d.p[q]) d.p[q][m * d.ld[q] + j] = v;
+}
+
+// Generator epilogue: heads [M, ldh] = (joint_conf nJ | rot6d 6 | transl 3) -> rot_matrix (Gram-Schmidt, columns x,y,z),
+// transl - z_offset * R[:,0] evaluated in float64 like utils.translate_along_axis, joint_conf.
+__global__ void pose_finish_kernel(const float* heads, int64_t ldh, int nJ, int64_t M, float z_offset, float* rot,
+                                   float* transl, float* joint, float* rot6d) {
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    const float* h = heads + m * ldh;
+    for (int j = 0; j < nJ; ++j) joint[m * nJ + j] = h[j];
+    const float a0 = h[nJ], a1 = h[nJ + 1], a2 = h[nJ + 2], b0 = h[nJ + 3], b1 = h[nJ + 4], b2 = h[nJ + 5];
+    if (rot6d) {
+        float* r6 = rot6d + m * 6;
+        r6[0] = a0; r6[1] = a1; r6[2] = a2; r6[3] = b0; r6[4] = b1; r6[5] = b2;
+    }
+    const float na = fmaxf(sqrtf(a0 * a0 + a1 * a1 + a2 * a2), 1e-8f);
+    const float x0 = a0 / na, x1 = a1 / na, x2 = a2 / na;
+    float z0 = x1 * b2 - x2 * b1, z1 = x2 * b0 - x0 * b2, z2 = x0 * b1 - x1 * b0;
+    const float nz = fmaxf(sqrtf(z0 * z0 + z1 * z1 + z2 * z2), 1e-8f);
+    z0 /= nz; z1 /= nz; z2 /= nz;
+    const float y0 = z1 * x2 - z2 * x1, y1 = z2 * x0 - z0 * x2, y2 = z0 * x1 - z1 * x0;
+    float* r = rot + m * 9;
+    r[0] = x0; r[1] = y0; r[2] = z0;
+    r[3] = x1; r[4] = y1; r[5] = z1;
+    r[6] = x2; r[7] = y2; r[8] = z2;
+    const double off = (double)z_offset;
+    transl[m * 3 + 0] = (float)((double)h[nJ + 6] - (double)x0 * off);
+    transl[m * 3 + 1] = (float)((double)h[nJ + 7] - (double)x1 * off);
+    transl[m * 3 + 2] = (float)((double)h[nJ + 8] - (double)x2 * off);
+}
+
+// p[m] = sigmoid(X[m,:] . w + b)     (one warp per row, K = 512)
+__global__ void rowdot_sigmoid_kernel(const float* X, int64_t ldx, const float* w, const float* b, int K, int64_t M, float* p) {
+    const int64_t m = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (m >= M) return;
+    const float* x = X + m * ldx;
+    float s = 0.f;
+    for (int k = lane * 4; k < K; k += 128) {
+        const float4 xv = *reinterpret_cast<const float4*>(x + k), wv = *reinterpret_cast<const float4*>(w + k);
+        s = fmaf(xv.x, wv.x, s);
+        s = fmaf(xv.y, wv.y, s);
+        s = fmaf(xv.z, wv.z, s);
+        s = fmaf(xv.w, wv.w, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) p[m] = 1.f / (1.f + expf(-(s + b[0])));
+}
+
+}  // namespace dexgg
+
+using namespace dexgg;
+
+// ---------------------------------------------------------------- net handle
+struct BlockPack {
+    float *Wt, *sc, *sh, *W2, *sc2, *sh2;
+    int KT, has_x;
+};
+struct dexgg_net {
+    int kind, precision, latentD, nJ;
+    int n_blocks, n_tail, tailw, nbase, nh, n_params;
+    float *Wb, *bb, *in_a, *in_c, *tail_a, *tail_c, *Wh, *bh, *tmp_a, *tmp_c;
+    BlockPack blk[3];
+    void* arena;
+    size_t arena_bytes;
+};
+
+namespace {
+struct Layout {  // column ranges of one ResBlock's input
+    int bps_off, tail_off, x_off;  // x_off < 0: no previous-X segment
+};
+int n_expected(int kind) { return kind == DEXGG_NET_GENERATOR ? 38 : kind == DEXGG_NET_DISCRIMINATOR ? 34 : 48; }
+
+Layout block_layout(const dexgg_net* n, int b) {
+    const int zD = n->latentD, np = n->n_tail;
+    if (n->kind == DEXGG_NET_GENERATOR) return b == 0 ? Layout{zD, 0, -1} : Layout{zD, 0, zD + IN_BPS};  // cat[z,bps] / cat[X0,X]
+    if (n->kind == DEXGG_NET_DISCRIMINATOR) return b == 0 ? Layout{0, IN_BPS, -1} : Layout{0, IN_BPS, IN_BPS + np};  // cat[X0,X]
+    return b == 0 ? Layout{0, IN_BPS, -1} : Layout{HID, HID + IN_BPS, 0};  // evaluator: cat[X, X0]
+}
+
+inline unsigned nblk(int64_t n, int t = 256) { return (unsigned)((n + t - 1) / t); }
+
+int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
+    // input BatchNorm -> affine over [bps | tail]
+    const bool gen = n->kind == DEXGG_NET_GENERATOR;
+    const int n_in = IN_BPS + (gen ? 0 : n->n_tail);
+    bn_affine_kernel<<<nblk(n_in), 256, 0, st>>>(P[0], P[1], P[2], P[3], n_in, n->in_a, n->in_c);
+    DEXGG_CUDA_OK(cudaMemsetAsync(n->tail_a, 0, 2 * n->tailw * sizeof(float), st));
+    if (!gen) {
+        DEXGG_CUDA_OK(cudaMemcpyAsync(n->tail_a, n->in_a + IN_BPS, n->n_tail * 4, cudaMemcpyDeviceToDevice, st));
+        DEXGG_CUDA_OK(cudaMemcpyAsync(n->tail_c, n->in_c + IN_BPS, n->n_tail * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    for (int b = 0; b < n->n_blocks; ++b) {
+        const float* const* q = P + 4 + 14 * b;  // fc1.w fc1.b bn1.{w,b,rm,rv} fc2.w fc2.b bn2.{w,b,rm,rv} fc3.w fc3.b
+        const Layout L = block_layout(n, b);
+        const int fin = IN_BPS + n->n_tail + (L.x_off >= 0 ? HID : 0);
+        BlockPack& B = n->blk[b];
+        DEXGG_CUDA_OK(cudaMemsetAsync(B.Wt, 0, (size_t)NCAT * B.KT * 4, st));
+        for (int part = 0; part < 2; ++part) {
+            const float* w = part == 0 ? q[0] : q[12];
+            const float* bias = part == 0 ? q[1] : q[13];
+            const int rows = part == 0 ? INNER : HID, r0 = part == 0 ? 0 : INNER;
+            float* wb = n->Wb + (size_t)(b * NCAT + r0) * IN_BPS;
+            pack_cols_kernel<<<nblk((int64_t)rows * IN_BPS), 256, 0, st>>>(wb, IN_BPS, 0, w, fin, L.bps_off, IN_BPS, rows, n->in_a);
+            fold_bias_kernel<<<nblk(rows, 8), 256, 0, st>>>(n->bb + b * NCAT + r0, bias, w, fin, L.bps_off, IN_BPS, rows, n->in_c);
+            float* wt = B.Wt + (size_t)r0 * B.KT;
+            int col = 0;
+            if (L.x_off >= 0) {
+                pack_cols_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT, 0, w, fin, L.x_off, HID, rows, nullptr);
+                col = HID;
+            }
+            pack_cols_kernel<<<nblk((int64_t)rows * n->n_tail), 256, 0, st>>>(wt, B.KT, col, w, fin, L.tail_off, n->n_tail, rows, nullptr);
+        }
+        bn_affine_kernel<<<nblk(INNER), 256, 0, st>>>(q[2], q[3], q[4], q[5], INNER, B.sc, B.sh);
+        fill_kernel<<<nblk(HID), 256, 0, st>>>(B.sc + INNER, 1.f, HID);
+        fill_kernel<<<nblk(HID), 256, 0, st>>>(B.sh + INNER, 0.f, HID);
+        DEXGG_CUDA_OK(cudaMemcpyAsync(B.W2, q[6], (size_t)HID * INNER * 4, cudaMemcpyDeviceToDevice, st));
+        bn_affine_kernel<<<nblk(HID), 256, 0, st>>>(q[8], q[9], q[10], q[11], HID, n->tmp_a, n->tmp_c);
+        affine_bias_kernel<<<nblk(HID), 256, 0, st>>>(n->tmp_a, n->tmp_c, q[7], HID, B.sc2, B.sh2);
+    }
+    const float* const* h = P + 4 + 14 * n->n_blocks;
+    if (gen) {  // rows: joint_conf (nJ) | rot6d (6) | transl (3)
+        const int rows[3] = {n->nJ, 6, 3};
+        int r = 0;
+        for (int i = 0; i < 3; ++i) {
+            DEXGG_CUDA_OK(cudaMemcpyAsync(n->Wh + (size_t)r * HID, h[2 * i], (size_t)rows[i] * HID * 4, cudaMemcpyDeviceToDevice, st));
+            DEXGG_CUDA_OK(cudaMemcpyAsync(n->bh + r, h[2 * i + 1], rows[i] * 4, cudaMemcpyDeviceToDevice, st));
+            r += rows[i];
+        }
+    } else {
+        DEXGG_CUDA_OK(cudaMemcpyAsync(n->Wh, h[0], HID * 4, cudaMemcpyDeviceToDevice, st));
+        DEXGG_CUDA_OK(cudaMemcpyAsync(n->bh, h[1], 4, cudaMemcpyDeviceToDevice, st));
+    }
+    DEXGG_LAUNCH_OK("net packing kernels");
+    return DEXGG_OK;
+}
+
+struct Carver {
+    char* p;
+    size_t used = 0;
+    template <typename T>
+    T* take(size_t n) {
+        T* r = p ? reinterpret_cast<T*>(p + used) : nullptr;
+        used += align_up(n * sizeof(T), 256);
+        return r;
+    }
+};
+
+void carve_net(dexgg_net* n, Carver& c) {
+    n->Wb = c.take<float>((size_t)n->nbase * IN_BPS);
+    n->bb = c.take<float>(n->nbase);
+    n->in_a = c.take<float>(IN_BPS + 64);
+    n->in_c = c.take<float>(IN_BPS + 64);
+    n->tail_a = c.take<float>(2 * n->tailw);
+    n->tail_c = n->tail_a ? n->tail_a + n->tailw : nullptr;
+    n->tmp_a = c.take<float>(HID);
+    n->tmp_c = c.take<float>(HID);
+    n->Wh = c.take<float>((size_t)32 * HID);
+    n->bh = c.take<float>(32);
+    for (int b = 0; b < n->n_blocks; ++b) {
+        BlockPack& B = n->blk[b];
+        B.has_x = block_layout(n, b).x_off >= 0;
+        B.KT = (B.has_x ? HID : 0) + n->tailw;
+        B.Wt = c.take<float>((size_t)NCAT * B.KT);
+        B.sc = c.take<float>(NCAT);
+        B.sh = c.take<float>(NCAT);
+        B.W2 = c.take<float>((size_t)HID * INNER);
+        B.sc2 = c.take<float>(HID);
+        B.sh2 = c.take<float>(HID);
+    }
+}
+
+// workspace of one forward call
+struct FwdWs {
+    float *base, *tail, *T, *XT0, *XT1, *H;
+    int64_t mc;
+};
+size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w) {
+    Carver c{static_cast<char*>(ws)};
+    const int64_t mc = M < CHUNK_ROWS ? M : CHUNK_ROWS;
+    w.mc = mc;
+    w.base = c.take<float>((size_t)n_obj * n->nbase);
+    w.tail = c.take<float>((size_t)mc * n->tailw);
+    w.T = c.take<float>((size_t)mc * NCAT);
+    w.XT0 = c.take<float>((size_t)mc * (HID + n->tailw));
+    w.XT1 = c.take<float>((size_t)mc * (HID + n->tailw));
+    w.H = c.take<float>((size_t)mc * 32);
+    return c.used;
+}
+
+int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int64_t rows_per_obj, int64_t M, const void* ws,
+              size_t ws_bytes) {
+    DEXGG_REQUIRE(n && n->kind == kind, "forward: wrong or null net handle");
+    DEXGG_REQUIRE(n_obj >= 0 && rows_per_obj >= 1 && M == n_obj * rows_per_obj, "forward: M (%lld) must equal n_obj*rows_per_obj (%lld*%lld)",
+                  (long long)M, (long long)n_obj, (long long)rows_per_obj);
+    DEXGG_REQUIRE(rows_per_obj < (1ll << 31) && M < (1ll << 40), "forward: sizes too large");
+    DEXGG_REQUIRE(M == 0 || bps, "forward: null bps");
+    FwdWs w;
+    const size_t need = carve_ws(n, M, n_obj, nullptr, w);
+    if (M > 0 && (!ws || ws_bytes < need)) {
+        set_error("forward: workspace of %zu bytes needed, %zu given", need, ws_bytes);
+        return DEXGG_E_WORKSPACE;
+    }
+    return DEXGG_OK;
+}
+
+// base[n_obj, nbase] = bps · Wbᵀ + bb    (once per object; for row-wise inputs n_obj == M)
+int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, float* base, cudaStream_t st) {
+    LinearF32 p;
+    p.A = bps; p.lda = IN_BPS; p.W = n->Wb; p.ldw = IN_BPS;
+    p.M = (int)n_obj; p.N = n->nbase; p.K = IN_BPS; p.C = base; p.ldc = n->nbase;
+    p.ep.bias = n->bb;
+    return linear_f32(p, st);
+}
+
+// One ResBlock on a chunk: T = lrelu(sc*(A·Wtᵀ + base) + sh);  Xout = lrelu(T[:,256:] + sc2*(T[:,:256]·W2ᵀ) + sh2)
+int run_block(const dexgg_net* n, int b, const float* A, int64_t lda, const float* base, int rows_per_obj, int64_t row0,
+              int64_t mc, float* T, float* Xout, int64_t ldx, cudaStream_t st) {
+    const BlockPack& B = n->blk[b];
+    LinearF32 p;
+    p.A = A; p.lda = lda; p.W = B.Wt; p.ldw = B.KT; p.M = (int)mc; p.N = NCAT; p.K = B.KT; p.C = T; p.ldc = NCAT;
+    p.ep.base = base + b * NCAT; p.ep.ldbase = n->nbase; p.ep.rows_per_obj = rows_per_obj; p.ep.row0 = row0;
+    p.ep.scale = B.sc; p.ep.shift = B.sh; p.ep.act = 1;
+    int rc = linear_f32(p, st);
+    if (rc) return rc;
+    LinearF32 q;
+    q.A = T; q.lda = NCAT; q.W = B.W2; q.ldw = INNER; q.M = (int)mc; q.N = HID; q.K = INNER; q.C = Xout; q.ldc = ldx;
+    q.ep.scale = B.sc2; q.ep.shift = B.sh2; q.ep.residual = T + INNER; q.ep.ldr = NCAT; q.ep.act = 1;
+    return linear_f32(q, st);
+}
+}  // namespace
+
+extern "C" int dexgg_net_create(int kind, const float* const* params, int n_params, int latent_dim, int n_joints,
+                                int precision, void* stream, dexgg_net** out) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(out && params, "net_create: null argument");
+    DEXGG_REQUIRE(kind >= DEXGG_NET_GENERATOR && kind <= DEXGG_NET_EVALUATOR, "net_create: unknown kind %d", kind);
+    DEXGG_REQUIRE(n_params == n_expected(kind), "net_create: kind %d takes %d parameter tensors, got %d", kind, n_expected(kind), n_params);
+    DEXGG_REQUIRE(precision == DEXGG_PRECISION_FP32, "net_create: unsupported precision %d", precision);
+    DEXGG_REQUIRE(latent_dim >= 1 && latent_dim <= 16 && n_joints >= 1 && n_joints <= 20, "net_create: latent_dim/n_joints out of range");
+    for (int i = 0; i < n_params; ++i) DEXGG_REQUIRE(params[i], "net_create: parameter %d is null", i);
+    dexgg_net* n = new (std::nothrow) dexgg_net();
+    DEXGG_REQUIRE(n, "net_create: out of host memory");
+    n->kind = kind; n->precision = precision; n->latentD = latent_dim; n->nJ = n_joints; n->n_params = n_params;
+    n->n_blocks = kind == DEXGG_NET_EVALUATOR ? 3 : 2;
+    n->n_tail = kind == DEXGG_NET_GENERATOR ? latent_dim : kind == DEXGG_NET_DISCRIMINATOR ? 12 + n_joints : 12;
+    n->tailw = n->n_tail <= 16 ? 16 : 32;
+    n->nbase = NCAT * n->n_blocks;
+    n->nh = kind == DEXGG_NET_GENERATOR ? n_joints + 9 : 1;
+    Carver sz{nullptr};
+    carve_net(n, sz);
+    n->arena_bytes = sz.used;
+    cudaError_t e = cudaMalloc(&n->arena, n->arena_bytes);
+    if (e != cudaSuccess) {
+        set_error("net_create: cudaMalloc(%zu) failed: %s", n->arena_bytes, cudaGetErrorString(e));
+        delete n;
+        return DEXGG_E_CUDA;
+    }
+    Carver c{static_cast<char*>(n->arena)};
+    carve_net(n, c);
+    int rc = pack_net(n, params, static_cast<cudaStream_t>(stream));
+    if (rc != DEXGG_OK) {
+        cudaFree(n->arena);
+        delete n;
+        return rc;
+    }
+    *out = n;
+    return DEXGG_OK;
+}
+
+extern "C" int dexgg_net_update(dexgg_net* net, const float* const* params, int n_params, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(net && params && n_params == net->n_params, "net_update: bad arguments");
+    return pack_net(net, params, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" void dexgg_net_destroy(dexgg_net* net) {
+    if (!net) return;
+    cudaFree(net->arena);
+    delete net;
+}
+
+extern "C" size_t dexgg_net_workspace_bytes(const dexgg_net* net, int64_t M, int64_t n_obj) {
+    if (!net || M < 0 || n_obj < 0) return 0;
+    FwdWs w;
+    return carve_ws(net, M, n_obj, nullptr, w);
+}
+
+extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, int64_t n_obj, int64_t rows_per_obj,
+                                       const float* z, int64_t M, float z_offset, float* rot, float* transl, float* joint,
+                                       float* rot6d, void* workspace, size_t workspace_bytes, void* stream) {
+    DEXGG_ARCH_OK();
+    int rc = check_fwd(net, DEXGG_NET_GENERATOR, bps, n_obj, rows_per_obj, M, workspace, workspace_bytes);
+    if (rc) return rc;
+    if (M == 0) return DEXGG_OK;
+    DEXGG_REQUIRE(z && rot && transl && joint, "generator_forward: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    FwdWs w;
+    carve_ws(net, M, n_obj, workspace, w);
+    if ((rc = compute_base(net, bps, n_obj, w.base, st))) return rc;
+    const int tw = net->tailw, zD = net->latentD, ldx = HID + tw;
+    for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
+        const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
+        TailDst d{{w.tail, w.XT0 + HID, nullptr}, {tw, ldx, 0}};
+        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(z + r0 * zD, zD, nullptr, 0, nullptr, 0, nullptr, nullptr, tw, mc, d);
+        if ((rc = run_block(net, 0, w.tail, tw, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
+        if ((rc = run_block(net, 1, w.XT0, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT1, ldx, st))) return rc;
+        LinearF32 h;
+        h.A = w.XT1; h.lda = ldx; h.W = net->Wh; h.ldw = HID; h.M = (int)mc; h.N = net->nh; h.K = HID; h.C = w.H; h.ldc = 32;
+        h.ep.bias = net->bh;
+        if ((rc = linear_f32(h, st))) return rc;
+        pose_finish_kernel<<<nblk(mc, 128), 128, 0, st>>>(w.H, 32, net->nJ, mc, z_offset, rot + r0 * 9, transl + r0 * 3,
+                                                         joint + r0 * net->nJ, rot6d ? rot6d + r0 * 6 : nullptr);
+    }
+    DEXGG_LAUNCH_OK("generator_forward kernels");
+    return DEXGG_OK;
+}
+
+static int score_forward(const dexgg_net* net, int kind, const float* bps, int64_t n_obj, int64_t rows_per_obj,
+                         const float* rot, const float* transl, const float* joint, int64_t M, float* p, void* workspace,
+                         size_t workspace_bytes, void* stream) {
+    DEXGG_ARCH_OK();
+    int rc = check_fwd(net, kind, bps, n_obj, rows_per_obj, M, workspace, workspace_bytes);
+    if (rc) return rc;
+    if (M == 0) return DEXGG_OK;
+    DEXGG_REQUIRE(rot && transl && p && (kind == DEXGG_NET_EVALUATOR || joint), "score forward: null pointer");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    FwdWs w;
+    carve_ws(net, M, n_obj, workspace, w);
+    if ((rc = compute_base(net, bps, n_obj, w.base, st))) return rc;
+    const int tw = net->tailw, ldx = HID + tw, nJ = net->nJ;
+    const bool disc = kind == DEXGG_NET_DISCRIMINATOR;
+    for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
+        const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
+        TailDst d{{w.tail, w.XT0 + HID, w.XT1 + HID}, {tw, ldx, ldx}};
+        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(rot + r0 * 9, 9, transl + r0 * 3, 3, disc ? joint + r0 * nJ : nullptr,
+                                                       disc ? nJ : 0, net->tail_a, net->tail_c, tw, mc, d);
+        if ((rc = run_block(net, 0, w.tail, tw, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
+        if ((rc = run_block(net, 1, w.XT0, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT1, ldx, st))) return rc;
+        const float* X = w.XT1;
+        if (!disc) {
+            if ((rc = run_block(net, 2, w.XT1, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
+            X = w.XT0;
+        }
+        rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(X, ldx, net->Wh, net->bh, HID, mc, p + r0);
+    }
+    DEXGG_LAUNCH_OK("score forward kernels");
+    return DEXGG_OK;
+}
+
+extern "C" int dexgg_evaluator_forward(const dexgg_net* net, const float* bps, int64_t n_obj, int64_t rows_per_obj,
+                                       const float* rot, const float* transl, int64_t M, float* p, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+    return score_forward(net, DEXGG_NET_EVALUATOR, bps, n_obj, rows_per_obj, rot, transl, nullptr, M, p, workspace,
+                         workspace_bytes, stream);
+}
+
+extern "C" int dexgg_discriminator_forward(const dexgg_net* net, const float* bps, int64_t n_obj, int64_t rows_per_obj,
+                                           const float* rot, const float* transl, const float* joint, int64_t M, float* p,
+                                           void* workspace, size_t workspace_bytes, void* stream) {
+    return score_forward(net, DEXGG_NET_DISCRIMINATOR, bps, n_obj, rows_per_obj, rot, transl, joint, M, p, workspace,
+                         workspace_bytes, stream);
+}

@@ -68,6 +68,83 @@ int dexgg_bps_encode(const float* basis, int P, const float* pts, const int64_t*
 int dexgg_bps_encode_host(const float* basis, int P, const float* pts, const int64_t* offsets, int B, float* dists,
                           int32_t* idx, int flags);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Stages 2-3 — DexGenerator / Discriminator / DexEvaluator forward (eval-mode BatchNorm).
+ * Replace Generator.forward (DexGanGrasp/models/networks.py:88-103) + utils.rot_matrix_from_ortho6d
+ * (utils/utils.py:380-394) + utils.translate_along_axis (utils/utils.py:19-48) as driven by
+ * DexGANGrasp.generate_poses (networks.py:223-255); DexEvaluator.forward (networks.py:315-337) as driven by
+ * DexGanGrasp.evaluate_grasps / filter_grasps (models/dexgangrasp.py:367-442); Discriminator.forward
+ * (networks.py:148-159) as driven by filter_grasps_discriminator (dexgangrasp.py:444-493).
+ *
+ * A net handle owns packed copies of the weights (input BatchNorm folded into the BPS columns, fc1 and fc3 of every
+ * ResBlock fused into one 768-row matrix, bn1/bn2 folded into per-column affines).  `params` lists the module's
+ * float tensors in state_dict order WITHOUT num_batches_tracked:
+ *   generator (38):     gen_bn1.{weight,bias,running_mean,running_var}, gen_rb1.*, gen_rb2.*, gen_joint_conf.{weight,bias},
+ *                       gen_rot.{weight,bias}, gen_transl.{weight,bias}
+ *   discriminator (34): disc_bn1.*, disc_rb1.*, disc_rb2.*, out_success.{weight,bias}
+ *   evaluator (48):     bn1.*, rb1.*, rb2.*, rb3.*, out_success.{weight,bias}
+ *   with ResBlock = fc1.{weight,bias}, bn1.{weight,bias,running_mean,running_var}, fc2.{weight,bias}, bn2.{...},
+ *   fc3.{weight,bias} (14 tensors).  Call dexgg_net_update after the parameters change (optimizer step,
+ *   load_state_dict); the handle keeps no reference to the caller's tensors.
+ *
+ * Rows and objects: the BPS encoding is given once per OBJECT (bps [n_obj,4096]); row m belongs to object
+ * m / rows_per_obj (the reference tiles the encoding instead, np.tile at dexgangrasp.py:403-404,509-510).  The 4096-wide part
+ * of every first-layer product is computed once per object.  rows_per_obj = 1 is the row-wise case (every row its
+ * own encoding: eval_batch, training-style batches).  M must equal n_obj * rows_per_obj.
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct dexgg_net dexgg_net;
+enum { DEXGG_NET_GENERATOR = 0, DEXGG_NET_DISCRIMINATOR = 1, DEXGG_NET_EVALUATOR = 2 };
+enum {
+    DEXGG_PRECISION_FP32 = 0, /* CUDA-core fp32: within 1e-4 abs of the reference's torch fp32 path */
+    DEXGG_PRECISION_BF16 = 1  /* tcgen05 bf16 operands, fp32 accumulation in TMEM */
+};
+
+int dexgg_net_create(int kind, const float* const* params, int n_params, int latent_dim, int n_joints, int precision,
+                     void* stream, dexgg_net** out);
+int dexgg_net_update(dexgg_net* net, const float* const* params, int n_params, void* stream);
+void dexgg_net_destroy(dexgg_net* net);
+size_t dexgg_net_workspace_bytes(const dexgg_net* net, int64_t M, int64_t n_obj);
+
+/* z [M,latent_dim] (torch.randn at networks.py:240 — the caller draws it, "same z" contract) ->
+ * rot [M,9] row-major 3x3 with columns (x,y,z), transl [M,3] already moved by -z_offset along the palm x axis,
+ * joint [M,n_joints]; rot6d [M,6] optional raw head output (NULL to skip). */
+int dexgg_generator_forward(const dexgg_net* net, const float* bps, int64_t n_obj, int64_t rows_per_obj, const float* z,
+                            int64_t M, float z_offset, float* rot, float* transl, float* joint, float* rot6d,
+                            void* workspace, size_t workspace_bytes, void* stream);
+/* p [M] = sigmoid(out_success(...)); joint_conf is not an evaluator input (networks.py:307-313). */
+int dexgg_evaluator_forward(const dexgg_net* net, const float* bps, int64_t n_obj, int64_t rows_per_obj, const float* rot,
+                            const float* transl, int64_t M, float* p, void* workspace, size_t workspace_bytes,
+                            void* stream);
+int dexgg_discriminator_forward(const dexgg_net* net, const float* bps, int64_t n_obj, int64_t rows_per_obj,
+                                const float* rot, const float* transl, const float* joint, int64_t M, float* p,
+                                void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Stage 4 — threshold + sort / top-k, per segment of rows_per_seg consecutive rows (one object each).
+ * Replaces p.sort(descending=True) / indices[sorted_score > thresh] of DexGanGrasp.filter_grasps
+ * (models/dexgangrasp.py:412-419): keeps p > thresh (strict), best first, equal scores by lower row index.
+ *   idx_out   [n_seg,k] i32 global row ids, -1 padded;  count_out [n_seg] i32 = min(#kept, k)
+ *   best_out  [n_seg] f32 (may be NULL) best score of the segment — the caller raises the reference's ValueError
+ *             when best < thresh (dexgangrasp.py:414-416);  score_out [n_seg,k] f32 (may be NULL).
+ * k = rows_per_seg gives the reference's full sorted order.  rows_per_seg <= 16384.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dexgg_filter_topk(const float* p, int64_t M, int64_t rows_per_seg, float thresh, int k, int32_t* idx_out,
+                      int32_t* count_out, float* best_out, float* score_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * One fused linear layer, fp32 CUDA cores:  C = act(scale * (A·Wᵀ + bias) + shift + residual)  [+ C if accumulate].
+ * Building block of the training step (nn.Linear forward, dgrad with trans_w, wgrad with trans_a) and of the nets above.
+ * A(m,k) = A[m*lda+k] (trans_a: A[k*lda+m]);  W(n,k) = W[n*ldw+k] (trans_w: W[k*ldw+n]);  act 1 = LeakyReLU(0.2).
+ * ---------------------------------------------------------------------------------------------------------- */
+int dexgg_linear_f32(const float* A, int64_t lda, int trans_a, const float* W, int64_t ldw, int trans_w, int M, int N,
+                     int K, const float* bias, const float* scale, const float* shift, const float* residual,
+                     int64_t ldr, int act, int accumulate, float* C, int64_t ldc, void* stream);
+
+/* rot6d -> rotation matrix (utils.rot_matrix_from_ortho6d, DexGanGrasp/utils/utils.py:380-394) and its backward
+ * (used by the generator training step, dexgangrasp.py:776 and losses.py:67).  r6 [M,6], rot / g_rot [M,9], g_r6 [M,6]. */
+int dexgg_rot6d_forward(const float* r6, int64_t M, float* rot, void* stream);
+int dexgg_rot6d_backward(const float* r6, const float* g_rot, int64_t M, float* g_r6, void* stream);
+
 /* FP32-pipe micro-benchmark used for the BPS roofline denominator: runs `iters` rounds of 8
  * independent FFMA (kind 0), FFMA2 (kind 1), FADD2 (kind 2) or FMNMX3 (kind 3) chains per thread on a full grid and
  * returns the elapsed milliseconds in *ms and the number of lane-operations executed in *lane_ops. */

@@ -1,0 +1,218 @@
+"""GPU parity of the generator / evaluator / discriminator forwards, rot6d, palm offset and the filter (all through the
+C ABI) against (1) golden outputs of the reference's own nn.Modules (tests/golden/nets_golden.npz) and (2) the CPU oracle
+(oracle/nets_oracle.py) on seeded inputs.  Tolerance for the fp32 mode: 1e-4 absolute (BASELINE.json north_star)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from dex_gan_grasp_b200 import _native, synth
+from oracle import nets_oracle as no
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+SEED = 7
+CFG = dict(latentD=5, n_hand_joints=12, is_train=False, gpu_ids=[0], model="dexgangrasp", is_wgan=False)
+
+
+def md(a, b):
+    a = a.detach().cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    b = b.detach().cpu().numpy() if torch.is_tensor(b) else np.asarray(b)
+    return float(np.max(np.abs(a.astype(np.float64).reshape(-1) - b.astype(np.float64).reshape(-1))))
+
+
+@pytest.fixture(scope="module")
+def model():
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    m = DexGanGrasp(dict(CFG))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    m.DexGANGrasp.eval()
+    m.DexEvaluator.eval()
+    return m
+
+
+def test_linear_kernel_vs_torch():
+    """The fused linear kernel in isolation, all operand layouts and the full epilogue, against torch fp32."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    L = _native.lib()
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for (M, N, K, ta, tw) in [(300, 768, 528, 0, 0), (64, 21, 512, 0, 0), (257, 130, 4101, 0, 0), (128, 4101, 256, 0, 1),
+                              (256, 4101, 300, 1, 1), (1, 1, 1, 0, 0), (1000, 512, 16, 0, 0)]:
+        A = torch.randn((K, M) if ta else (M, K), device="cuda", generator=g)
+        W = torch.randn((K, N) if tw else (N, K), device="cuda", generator=g) / K ** 0.5
+        bias, scale, shift = (torch.randn(N, device="cuda", generator=g) for _ in range(3))
+        res = torch.randn((M, N), device="cuda", generator=g)
+        C = torch.randn((M, N), device="cuda", generator=g)
+        C0 = C.clone()
+        Am = A.t() if ta else A
+        Wm = W.t() if tw else W
+        ref = torch.nn.functional.leaky_relu((Am.double() @ Wm.double().t() + bias.double()) * scale.double() + shift.double()
+                                             + res.double(), 0.2) + C0.double()
+        _native.check(L.dexgg_linear_f32(A.data_ptr(), A.stride(0), ta, W.data_ptr(), W.stride(0), tw, M, N, K, bias.data_ptr(),
+                                         scale.data_ptr(), shift.data_ptr(), res.data_ptr(), N, 1, 1, C.data_ptr(), N, None))
+        torch.cuda.synchronize()
+        assert md(C, ref) < 2e-5 * max(1.0, float(ref.abs().max())), (M, N, K, ta, tw)
+
+
+def test_rowwise_forward_vs_reference_golden(model, eval_batch, nets_golden):
+    """Config C2 shape: data/eval_batch.pth, every row its own BPS encoding (rows_per_obj = 1)."""
+    bps = torch.from_numpy(eval_batch["bps_object"]).cuda()
+    z = torch.from_numpy(nets_golden["A/z"]).cuda()
+    out = model.DexGANGrasp.generator(z, bps)  # nn.Module surface: dict with rot_6D / transl / joint_conf / z
+    assert set(out) == {"rot_6D", "transl", "joint_conf", "z"}
+    assert md(out["rot_6D"], nets_golden["A/rot_6D"]) < TOL
+    assert md(out["joint_conf"], nets_golden["A/joint_conf"]) < TOL
+    rot, transl, joint, _ = model.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
+    assert md(rot, nets_golden["A/rot_matrix"]) < TOL and md(transl, nets_golden["A/transl"]) < TOL
+    from dex_gan_grasp_b200 import utils
+    assert md(utils.rot_matrix_from_ortho6d(out["rot_6D"]), nets_golden["A/rot_matrix"]) < TOL
+    p = model.DexEvaluator({"bps_object": bps, "rot_matrix": torch.from_numpy(nets_golden["A/rot_matrix"]),
+                            "transl": torch.from_numpy(nets_golden["A/transl"])})
+    assert p.shape == (64, 1) and md(p, nets_golden["A/p_eva"]) < TOL
+    real = {k: torch.from_numpy(eval_batch[k]) for k in ("bps_object", "rot_matrix", "transl", "joint_conf")}  # f64 inputs
+    assert md(model.DexGANGrasp.discriminator(real), nets_golden["A/p_disc_real"]) < TOL
+    assert md(model.DexEvaluator(real), nets_golden["A/p_eva_real"]) < TOL
+    fake = {"bps_object": bps, "rot_matrix": torch.from_numpy(nets_golden["A/rot_matrix"]),
+            "transl": torch.from_numpy(nets_golden["A/transl"]), "joint_conf": torch.from_numpy(nets_golden["A/joint_conf"])}
+    assert md(model.DexGANGrasp.discriminator(fake), nets_golden["A/p_disc_fake"]) < TOL
+
+
+def test_shared_bps_hoisted_path_and_filter(model, nets_golden):
+    """Config C1 shape: one object's encoding, n latent samples; the BPS projection is hoisted (once per object)."""
+    z = torch.from_numpy(nets_golden["B/z"]).cuda()
+    bps = torch.from_numpy(nets_golden["B/bps"]).cuda()  # [1,4096]
+    rot, transl, joint, _ = model.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
+    assert md(rot, nets_golden["B/rot_matrix"]) < TOL and md(transl, nets_golden["B/transl"]) < TOL
+    assert md(joint, nets_golden["B/joint_conf"]) < TOL
+    grasps = {"rot_matrix": nets_golden["B/rot_matrix"].copy(), "transl": nets_golden["B/transl"].copy(),
+              "joint_conf": nets_golden["B/joint_conf"].copy(), "z": nets_golden["B/z"].copy()}
+    p = model.evaluate_grasps(nets_golden["B/bps"], dict(grasps))
+    assert p.shape == (256,) and md(p, nets_golden["B/p_eva"]) < TOL
+    thr = float(nets_golden["B/thresh_med"])
+    f = model.filter_grasps(nets_golden["B/bps"], grasps, thresh=thr)
+    assert "bps_object" in grasps and grasps["bps_object"].shape == (256, 4096)  # reference side effect (dexgangrasp.py:408)
+    assert set(f) == {"rot_matrix", "transl", "joint_conf", "z", "bps_object"}
+    # same kept rows in the same order as the reference, rows whose score is within TOL of the threshold excluded
+    pg = nets_golden["B/p_eva"]
+    sure = np.abs(pg - thr) > TOL
+    kept_ref = [i for i in nets_golden["B/kept_med"] if sure[i]]
+    kept = []
+    for row in f["z"]:
+        i = int(np.where((nets_golden["B/z"] == row).all(1))[0][0])
+        if sure[i]:
+            kept.append(i)
+    gaps_ok = all(abs(pg[a] - pg[b]) < 2 * TOL for a, b in zip(kept, kept_ref) if a != b)  # near-equal scores may swap
+    assert len(kept) == len(kept_ref) and gaps_ok
+    assert f["bps_object"].shape == (len(f["z"]), 4096) and f["rot_matrix"].shape[1:] == (3, 3)
+    with pytest.raises(ValueError):
+        model.filter_grasps(nets_golden["B/bps"], dict(grasps), thresh=1.5)
+    assert len(model.filter_grasps(nets_golden["B/bps"], dict(grasps), thresh=-1)["z"]) == 256  # pure sort (dexafford_prompt.py:198)
+
+
+def test_wrapper_generate_matches_oracle_with_same_z(model, bps_golden):
+    """generate_grasps draws z with torch.randn on the device exactly like networks.py:240; with that z the CPU oracle
+    must give the same grasps; then filter_grasps_discriminator against the oracle discriminator."""
+    sd_gan, sd_eva = synth.synth_gan_state_dict(SEED), synth.synth_eva_state_dict(SEED)
+    bps = bps_golden["mustard_bottle/bps"]
+    torch.manual_seed(123)
+    g = model.generate_grasps(bps, n_samples=100, return_arr=True)  # dexgangrasp_offline-style C1
+    assert g["rot_matrix"].shape == (100, 3, 3) and g["transl"].dtype == np.float32 and g["z"].shape == (100, 5)
+    torch.manual_seed(123)
+    assert np.array_equal(torch.randn((100, 5), device="cuda").cpu().numpy(), g["z"])
+    o = no.generate_poses(sd_gan, torch.from_numpy(g["z"]), torch.from_numpy(np.tile(bps.squeeze(), (100, 1))), 0.025)
+    for k in ("rot_matrix", "transl", "joint_conf"):
+        assert md(g[k], o[k]) < TOL, k
+    with torch.no_grad():
+        pd = no.discriminator_forward(sd_gan, torch.from_numpy(np.tile(bps.squeeze(), (100, 1))), torch.from_numpy(o["rot_matrix"]),
+                                      torch.from_numpy(o["transl"]), torch.from_numpy(o["joint_conf"])).squeeze().numpy()
+    thr = float(np.median(pd))
+    f = model.filter_grasps_discriminator(bps, {k: g[k] for k in ("rot_matrix", "transl", "joint_conf", "z")}, thresh=thr)
+    n_sure = int((pd > thr + TOL).sum())
+    assert n_sure <= len(f["z"]) <= int((pd > thr - TOL).sum())
+
+
+def test_many_objects_rows_per_object(model, bps_golden):
+    """Batched form of config C3 at a size the oracle finishes in seconds: 7 objects x 300 samples in one call, plus the
+    chunked path (more rows than one internal chunk) checked for self-consistency."""
+    sd_gan, sd_eva = synth.synth_gan_state_dict(SEED), synth.synth_eva_state_dict(SEED)
+    names = list(bps_golden["names"])
+    bps = np.concatenate([bps_golden[f"{n}/bps"] for n in names])  # [7,4096]
+    S = 300
+    z = synth.synth_latents(7 * S, 5, seed=21)
+    rot, transl, joint, _ = model.DexGANGrasp.generator.native_forward(z, torch.from_numpy(bps), 0.025, False)
+    p = model.DexEvaluator.native_forward(torch.from_numpy(bps), rot, transl)
+    tiled = torch.from_numpy(np.repeat(bps, S, axis=0))
+    o = no.generate_poses(sd_gan, z, tiled, 0.025)
+    with torch.no_grad():
+        po = no.evaluator_forward(sd_eva, tiled, torch.from_numpy(o["rot_matrix"]), torch.from_numpy(o["transl"]))
+    assert md(rot, o["rot_matrix"]) < TOL and md(transl, o["transl"]) < TOL and md(joint, o["joint_conf"]) < TOL
+    assert md(p, po) < TOL
+    # chunking: 2 objects x 40000 rows (> 32768-row chunk, chunk boundary inside an object) == same rows in small calls
+    S2 = 40000
+    z2 = synth.synth_latents(2 * S2, 5, seed=22)
+    r_big, t_big, j_big, _ = model.DexGANGrasp.generator.native_forward(z2, torch.from_numpy(bps[:2]), 0.025, False)
+    p_big = model.DexEvaluator.native_forward(torch.from_numpy(bps[:2]), r_big, t_big)
+    sl = slice(S2 - 500, S2 + 500)  # straddles the object boundary
+    for ob, lo, hi in ((0, S2 - 500, S2), (1, S2, S2 + 500)):
+        r_s, t_s, j_s, _ = model.DexGANGrasp.generator.native_forward(z2[lo:hi], torch.from_numpy(bps[ob:ob + 1]), 0.025, False)
+        p_s = model.DexEvaluator.native_forward(torch.from_numpy(bps[ob:ob + 1]), r_s, t_s)
+        assert torch.equal(r_s, r_big[lo:hi]) and torch.equal(t_s, t_big[lo:hi]) and torch.equal(p_s, p_big[lo:hi])
+
+
+def test_filter_topk_segments_vs_oracle():
+    L = _native.lib()
+    rng = np.random.default_rng(0)
+    for (nseg, S, k, thr) in [(5, 1000, 10, 0.5), (3, 257, 257, 0.2), (1, 16384, 100, 0.9), (4, 64, 8, 2.0)]:
+        p = rng.random(nseg * S).astype(np.float32)
+        p[rng.integers(0, nseg * S, nseg * S // 4)] = np.float32(0.75)  # many exact ties
+        pt = torch.from_numpy(p).cuda()
+        idx = torch.empty((nseg, k), dtype=torch.int32, device="cuda")
+        cnt = torch.empty((nseg,), dtype=torch.int32, device="cuda")
+        best = torch.empty((nseg,), dtype=torch.float32, device="cuda")
+        sc = torch.empty((nseg, k), dtype=torch.float32, device="cuda")
+        _native.check(L.dexgg_filter_topk(pt.data_ptr(), nseg * S, S, thr, k, idx.data_ptr(), cnt.data_ptr(), best.data_ptr(),
+                                          sc.data_ptr(), None))
+        io, co = no.segmented_topk(p, np.arange(nseg + 1) * S, thr, k)
+        assert np.array_equal(idx.cpu().numpy(), io) and np.array_equal(cnt.cpu().numpy(), co)
+        assert np.array_equal(best.cpu().numpy(), p.reshape(nseg, S).max(1))
+        m = io >= 0
+        assert np.array_equal(sc.cpu().numpy()[m], p[io[m]])
+
+
+def test_weights_follow_parameter_updates(model, eval_batch, nets_golden):
+    """The packed copies are re-derived when parameters change in place (optimizer step / load_state_dict)."""
+    bps = torch.from_numpy(eval_batch["bps_object"]).cuda()
+    z = torch.from_numpy(nets_golden["A/z"]).cuda()
+    before = model.DexGANGrasp.generator(z, bps)["transl"].clone()
+    with torch.no_grad():
+        model.DexGANGrasp.generator.gen_transl.bias.add_(1.0)
+    after = model.DexGANGrasp.generator(z, bps)["transl"]
+    assert md(after, before + 1.0) < 1e-6
+    model.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    assert md(model.DexGANGrasp.generator(z, bps)["transl"], before) == 0.0
+
+
+def test_checkpoint_layout_roundtrip(model, tmp_path):
+    """Checkpoint dict keys and state-dict keys are the reference's."""
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    cfg = dict(CFG, is_train=True, bce_weight=1.0, kl_coef=0.0, lr=1e-4, lr_gen=1e-4, lr_dis=1e-4, beta1=0.9, weight_decay=5e-4,
+               lr_policy="plateau", threshold_lr_policy_plateau=0.01, patience_lr_policy_plateau=3, weight_init_type="xavier",
+               init_gain=0.02, train_ffhgenerator=True, train_ffhevaluator=True, save_dir=str(tmp_path), load_path=str(tmp_path))
+    m = DexGanGrasp(cfg)
+    assert list(m.DexGANGrasp.state_dict().keys()) == list(synth.synth_gan_state_dict(SEED).keys())
+    assert list(m.DexEvaluator.state_dict().keys()) == list(synth.synth_eva_state_dict(SEED).keys())
+    m.save_dexgenerator("3", 3)
+    m.save_dexevaluator("3", 3)
+    ck = torch.load(tmp_path / "3_gen_net.pt")
+    assert set(ck) == {"epoch", "ffhgenerator_state_dict", "optim_ffhgenerator_state_dict", "scheduler_ffhgenerator_state_dict",
+                       "optim_ffhgan_generator_state_dict", "scheduler_ffhgan_generator_state_dict",
+                       "optim_ffhgan_discriminator_state_dict", "scheduler_ffhgan_discriminator_state_dict"}
+    assert set(torch.load(tmp_path / "3_eva_net.pt")) == {"epoch", "ffhevaluator_state_dict", "optim_ffhevaluator_state_dict",
+                                                         "scheduler_ffhevaluator_state_dict"}
+    m2 = DexGanGrasp(dict(cfg))
+    m2.load_dexgenerator(3)
+    m2.load_dexevaluator(3)
+    for a, b in zip(m.DexGANGrasp.state_dict().values(), m2.DexGANGrasp.state_dict().values()):
+        assert torch.equal(a, b)
