@@ -1,0 +1,295 @@
+#!/usr/bin/env python
+"""bench.py — grasps/sec of the DexGANGrasp hot path (BPS -> DexGenerator -> DexEvaluator -> top-k) on B200.
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): 1024 synthetic single-view point clouds of
+2048 points x 1000 latent samples per cloud -> evaluator -> per-object top-10 above threshold 0.5.  One process per GPU;
+every rank runs the full workload on its own objects (no data-path collective) -> "scaling": "weak".
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--precision fp32|bf16] [--impl ours|reference]
+  torchrun --nproc-per-node N bench.py --gpus N ...
+
+`--impl reference` times the CPU restatement of the reference path (oracle/: C BPS + torch-CPU networks, all host cores)
+on a bounded sample of the same workload.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+N_CLOUDS, N_POINTS, N_SAMPLES, TOPK, THRESH, SEED = 1024, 2048, 1000, 10, 0.5, 7
+MAC_PER_GRASP, MAC_PER_OBJECT = 1_881_600, 15_728_640  # hoisted algorithm (SURVEY.md §8a note H)
+METRIC = "grasps/sec (BPS->DexGenerator->DexEvaluator->top-k)"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=os.environ.get("DEXGG_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--clouds", type=int, default=N_CLOUDS)
+    ap.add_argument("--samples", type=int, default=N_SAMPLES)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+# --------------------------------------------------------------------------------------------- CPU reference arm
+def cpu_reference_sample(n_objects, n_samples, n_points, seed0, repeats=1):
+    """The reference's per-object loop (dexgangrasp_offline.py:147-162 / dexgangrasp_real_robot.py:139-150) restated on
+    the host: BPS (oracle/bps_oracle.c, all cores) -> np.tile -> generator -> rot6d -> palm offset -> evaluator ->
+    sort / threshold.  Returns (grasps, seconds, cores)."""
+    from dex_gan_grasp_b200 import synth
+    from oracle import nets_oracle as no
+    so = os.path.join(REPO, "oracle", "libdexgg_oracle.so")
+    if not os.path.exists(so):
+        subprocess.check_call(["make", "-C", os.path.join(REPO, "oracle")])
+    lib = ctypes.CDLL(so)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    basis = np.load(os.path.join(REPO, "dex_gan_grasp_b200", "basis_point_set.npy")).astype(np.float32)
+    sd_gan, sd_eva = synth.synth_gan_state_dict(SEED), synth.synth_eva_state_dict(SEED)
+    clouds = [synth.synth_cloud(n_points, seed0 + i) for i in range(n_objects)]
+    zs = [synth.synth_latents(n_samples, 5, seed=seed0 + i) for i in range(n_objects)]
+    vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        kept = 0
+        for c, z in zip(clouds, zs):
+            d = np.empty(4096, np.float32)
+            idx = np.empty(4096, np.int32)
+            lib.dexgg_oracle_bps_encode_mt(vp(basis), 4096, vp(c), len(c), vp(d), vp(idx), min(cores, 256))
+            bps_t = torch.from_numpy(np.tile(d, (n_samples, 1)))
+            g = no.generate_poses(sd_gan, z, bps_t, 0.025)
+            try:
+                f, _ = no.filter_grasps(sd_eva, d, g, THRESH)
+                kept += min(TOPK, len(f["transl"]))
+            except ValueError:
+                pass
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return n_objects * n_samples, best, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    n_obj = 8
+    times = []
+    for i in range(args.warmup + args.steps):
+        g, dt, cores = cpu_reference_sample(n_obj, args.samples, N_POINTS, 1000 + 17 * i)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1e3 * float(np.mean(times))
+    val = n_obj * args.samples / (ms * 1e-3)
+    sample = f"{n_obj} objects x {args.samples} z per step (of {args.clouds} x {args.samples})"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "grasps/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C3 batched inference: synthetic clouds (2048 pts) x 1000 latent samples -> evaluator top-10",
+                       "clouds": args.clouds, "points": N_POINTS, "samples_per_cloud": args.samples, "topk": TOPK, "thresh": THRESH},
+            "cpu_baseline": {"value": val, "unit": "grasps/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "grasps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------- our arm
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    import torch.distributed as dist
+    from dex_gan_grasp_b200 import _native, synth
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    from dex_gan_grasp_b200.pipeline import GraspPipeline
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L = _native.lib()
+    _native.check(L.dexgg_device_check())
+    dev = torch.device("cuda", local)
+    B, S = args.clouds, args.samples
+    M = B * S
+
+    cfg = dict(latentD=5, n_hand_joints=12, is_train=False, gpu_ids=[local], model="dexgangrasp", is_wgan=False,
+               precision=args.precision)
+    model = DexGanGrasp(cfg)
+    model.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    model.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    pipe = GraspPipeline(model.DexGANGrasp, model.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025)
+
+    clouds_h = torch.from_numpy(synth.synth_clouds(B, N_POINTS, seed0=1000 + 100000 * rank)).pin_memory()
+    z_h = torch.randn((M, 5), generator=torch.Generator().manual_seed(1234 + rank)).pin_memory()
+    clouds_d, z_d = clouds_h.to(dev), z_h.to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (`value`) ----
+    for _ in range(args.warmup):
+        pipe.run_device(clouds_d, z_d, S)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    n0 = L.dexgg_launch_count()
+    for e0, e1 in ev:
+        flush.fill_(1)  # L2 flush between timed iterations (outside the event pair)
+        e0.record()
+        out = pipe.run_device(clouds_d, z_d, S)
+        e1.record()
+    barrier()
+    launches = (L.dexgg_launch_count() - n0) // max(args.steps, 1)
+    clocks = sampler.stop()
+    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    kept = int(out["count"].sum().item())
+
+    # ---- end to end through the public API with host buffers (`e2e`) ----
+    for _ in range(2):
+        pipe.run_host(clouds_h, z_h, S)
+    barrier()
+    t_e2e = []
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res, h2d, d2h = pipe.run_host(clouds_h, z_h, S)
+        torch.cuda.synchronize()
+        t_e2e.append(time.perf_counter() - t0)
+    barrier()
+    ms_e2e = 1e3 * float(np.mean(t_e2e))
+
+    # ---- per-stage device times (one instrumented step) and the roofline of the dominant kernel ----
+    def timed(fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flush.fill_(1)
+        a.record()
+        r = fn()
+        b.record()
+        b.synchronize()
+        return r, a.elapsed_time(b)
+    enc, t_bps = timed(lambda: pipe.encode(clouds_d))
+    (rot, transl, joint, _), t_gen = timed(lambda: model.DexGANGrasp.generator.native_forward(z_d, enc, 0.025, False))
+    p, t_eva = timed(lambda: model.DexEvaluator.native_forward(enc, rot, transl))
+    stages = {"bps_ms": t_bps, "generator_ms": t_gen, "evaluator_ms": t_eva, "filter_and_gather_ms": max(ms - t_bps - t_gen - t_eva, 0.0)}
+
+    pk, pk_src = peaks()
+    ms_probe, ops = ctypes.c_float(), ctypes.c_double()
+    _native.check(L.dexgg_fp32_pipe_probe(0, 2000, ctypes.byref(ms_probe), ctypes.byref(ops)))
+    fp32_tflops = 2 * ops.value / (ms_probe.value * 1e-3) / 1e12  # measured FFMA peak on this GPU, 2 FLOP per lane-op
+    mlp_flops = 2.0 * (MAC_PER_GRASP * M + MAC_PER_OBJECT * B)
+    mlp_tflops = mlp_flops / ((t_gen + t_eva) * 1e-3) / 1e12
+    bps_pairs = 4096.0 * B * N_POINTS
+    bps_lane_tops = 6 * bps_pairs / (t_bps * 1e-3) / 1e12
+    if args.precision == "bf16":
+        roof = {"bound": "tensor", "kernel": "linear_umma_kernel (tcgen05 bf16, all MLP layers)", "achieved": mlp_tflops,
+                "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": mlp_tflops / pk["bf16_tflops_sustained"],
+                "peak_source": pk_src + " bf16_tflops_sustained", "traffic": None}
+    else:
+        roof = {"bound": "fp32", "kernel": "linear_simt_kernel (fp32 CUDA-core mode, all MLP layers)", "achieved": mlp_tflops,
+                "peak": fp32_tflops, "unit": "TFLOP/s", "frac": mlp_tflops / fp32_tflops,
+                "peak_source": "FFMA probe measured in this run (dexgg_fp32_pipe_probe)", "traffic": None}
+    roof["bps_kernel"] = {"bound": "fp32", "kernel": "bps_nn_packed_kernel", "achieved": bps_lane_tops, "peak": fp32_tflops / 2,
+                          "unit": "T lane-op/s (6 per pair)", "frac": bps_lane_tops / (fp32_tflops / 2)}
+
+    # ---- max over ranks ----
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, ms_e2e_max = float(t[0]), float(t[1])
+
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        g, dt, cores = cpu_reference_sample(16, S, N_POINTS, 1000)
+        cpu = {"value": g / dt, "unit": "grasps/s", "cores": cores, "kind": "port",
+               "sample": f"first 16 objects x {S} z of the same workload, oracle/ (C BPS + torch-CPU networks), {dt:.2f} s"}
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": world * M / (ms_max * 1e-3), "unit": "grasps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (BPS) + " + ("bf16 tensor-core MMA / f32 accumulate (MLPs)" if args.precision == "bf16" else "f32 CUDA-core (MLPs)"),
+            "data": "synthetic",
+            "config": {"workload": "C3 batched inference: synthetic clouds (2048 pts) x 1000 latent samples -> evaluator top-10",
+                       "clouds_per_gpu": B, "points": N_POINTS, "samples_per_cloud": S, "topk": TOPK, "thresh": THRESH,
+                       "precision": args.precision, "l2": "256 MB flush write between timed iterations",
+                       "weights": "seeded synthetic state dicts (no trained checkpoints exist offline)"},
+            "e2e": {"value": world * M / (ms_e2e_max * 1e-3), "unit": "grasps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e_max},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "stages": stages, "cpu_baseline": cpu,
+            "kept_grasps_last_step": kept,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

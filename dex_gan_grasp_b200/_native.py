@@ -17,6 +17,7 @@ SIGNATURES = {
     "dexgg_version": (c_int, []),
     "dexgg_last_error": (ctypes.c_char_p, []),
     "dexgg_device_check": (c_int, []),
+    "dexgg_launch_count": (ctypes.c_ulonglong, []),
     "dexgg_bps_workspace_bytes": (c_size_t, [c_int, c_int]),
     "dexgg_bps_encode": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int,
                                  c_void_p, c_size_t, c_void_p]),

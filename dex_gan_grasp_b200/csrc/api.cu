@@ -1,11 +1,15 @@
 // Error state, device check and version of libdexgg.
 #include "common.cuh"
 
+#include <atomic>
 #include <mutex>
 
 namespace dexgg {
 
 static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+void count_launches(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+unsigned long long launches() { return g_launches.load(std::memory_order_relaxed); }
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -66,3 +70,4 @@ int sm_count() {
 extern "C" int dexgg_version(void) { return DEXGG_VERSION; }
 extern "C" const char* dexgg_last_error(void) { return dexgg::g_err; }
 extern "C" int dexgg_device_check(void) { return dexgg::device_check_cached(); }
+extern "C" unsigned long long dexgg_launch_count(void) { return dexgg::launches(); }

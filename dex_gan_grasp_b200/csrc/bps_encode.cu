@@ -317,7 +317,7 @@ static int launch_packed(const float* basis, int P, const float* pts, const int6
         attr_set = true;
     }
     dim3 grid((P + BPS_THREADS * R - 1) / (BPS_THREADS * R), B, nsplit);
-    bps_nn_packed_kernel<R><<<grid, BPS_THREADS, smem, st>>>(basis, P, pts, offsets, uniform_n, total, nsplit, keys);
+    bps_nn_packed_kernel<R><<<grid, BPS_THREADS, smem, st>>>(basis, P, pts, offsets, uniform_n, total, nsplit, keys); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("bps_nn_packed_kernel");
     return DEXGG_OK;
 }
@@ -343,7 +343,7 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
     if (total_points > 0 && max_cloud_points > 0) {
         if (flags & DEXGG_BPS_SCALAR) {
             dim3 grid((P + 127) / 128, B);
-            bps_nn_scalar_kernel<<<grid, 128, 0, st>>>(basis, P, pts, offsets, max_cloud_points, keys);
+            bps_nn_scalar_kernel<<<grid, 128, 0, st>>>(basis, P, pts, offsets, max_cloud_points, keys); ::dexgg::count_launches(1);
             DEXGG_LAUNCH_OK("bps_nn_scalar_kernel");
         } else {
             constexpr int R = 16;
@@ -364,7 +364,7 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
         }
     }
     const size_t tot = (size_t)B * P;
-    bps_finish_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(basis, P, pts, offsets, max_cloud_points, B, keys, dists, idx);
+    bps_finish_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(basis, P, pts, offsets, max_cloud_points, B, keys, dists, idx); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("bps_finish_kernel");
     return DEXGG_OK;
 }
@@ -426,10 +426,10 @@ extern "C" int dexgg_fp32_pipe_probe(int kind, int iters, float* ms, double* lan
     const int grid = sm_count() * 8, block = 256;
     for (int rep = 0; rep < 2; ++rep) {  // first launch warms up
         cudaEventRecord(e0);
-        if (kind == 0) fp32_probe_kernel<0><<<grid, block>>>(iters, out);
-        if (kind == 1) fp32_probe_kernel<1><<<grid, block>>>(iters, out);
-        if (kind == 2) fp32_probe_kernel<2><<<grid, block>>>(iters, out);
-        if (kind == 3) fp32_probe_kernel<3><<<grid, block>>>(iters, out);
+        if (kind == 0) { fp32_probe_kernel<0><<<grid, block>>>(iters, out); ::dexgg::count_launches(1); }
+        if (kind == 1) { fp32_probe_kernel<1><<<grid, block>>>(iters, out); ::dexgg::count_launches(1); }
+        if (kind == 2) { fp32_probe_kernel<2><<<grid, block>>>(iters, out); ::dexgg::count_launches(1); }
+        if (kind == 3) { fp32_probe_kernel<3><<<grid, block>>>(iters, out); ::dexgg::count_launches(1); }
         cudaEventRecord(e1);
         cudaEventSynchronize(e1);
     }

@@ -12,6 +12,7 @@ namespace dexgg {
 void set_error(const char* fmt, ...);  // thread-local message (api.cu)
 int device_check_cached();             // DEXGG_OK or DEXGG_E_ARCH / DEXGG_E_CUDA
 int sm_count();
+void count_launches(int n);         // kernels launched by this library (dexgg_launch_count)
 
 #define DEXGG_CUDA_OK(expr)                                                                              \
     do {                                                                                                 \

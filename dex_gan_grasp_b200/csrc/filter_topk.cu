@@ -108,7 +108,7 @@ extern "C" int dexgg_filter_topk(const float* p, int64_t M, int64_t rows_per_seg
         attr = true;
     }
     filter_sort_kernel<<<(unsigned)nseg, 256, smem, static_cast<cudaStream_t>(stream)>>>(p, rows_per_seg, M, thresh, k, npow2, idx_out,
-                                                                                         count_out, best_out, score_out);
+                                                                                         count_out, best_out, score_out); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("filter_sort_kernel");
     return DEXGG_OK;
 }

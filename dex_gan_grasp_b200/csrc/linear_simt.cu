@@ -174,10 +174,10 @@ static int launch_simt(const LinearF32& p, cudaStream_t st) {
     const int vw = (!p.trans_w && p.ldw % 4 == 0 && (reinterpret_cast<uintptr_t>(p.W) & 15) == 0) ? 1 : 0;
     const int vc = (p.ldc % 4 == 0 && (reinterpret_cast<uintptr_t>(p.C) & 15) == 0) ? 1 : 0;
     dim3 grid((p.M + SG_BM - 1) / SG_BM, (p.N + BN - 1) / BN);
-    if (!p.trans_a && !p.trans_w) linear_simt_kernel<BN, false, false><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc);
-    else if (!p.trans_a && p.trans_w) linear_simt_kernel<BN, false, true><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc);
-    else if (p.trans_a && !p.trans_w) linear_simt_kernel<BN, true, false><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc);
-    else linear_simt_kernel<BN, true, true><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc);
+    if (!p.trans_a && !p.trans_w) { linear_simt_kernel<BN, false, false><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc); ::dexgg::count_launches(1); }
+    else if (!p.trans_a && p.trans_w) { linear_simt_kernel<BN, false, true><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc); ::dexgg::count_launches(1); }
+    else if (p.trans_a && !p.trans_w) { linear_simt_kernel<BN, true, false><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc); ::dexgg::count_launches(1); }
+    else { linear_simt_kernel<BN, true, true><<<grid, SG_THREADS, 0, st>>>(p, va, vw, vc); ::dexgg::count_launches(1); }
     DEXGG_LAUNCH_OK("linear_simt_kernel");
     return DEXGG_OK;
 }

@@ -174,7 +174,7 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
     // input BatchNorm -> affine over [bps | tail]
     const bool gen = n->kind == DEXGG_NET_GENERATOR;
     const int n_in = IN_BPS + (gen ? 0 : n->n_tail);
-    bn_affine_kernel<<<nblk(n_in), 256, 0, st>>>(P[0], P[1], P[2], P[3], n_in, n->in_a, n->in_c);
+    bn_affine_kernel<<<nblk(n_in), 256, 0, st>>>(P[0], P[1], P[2], P[3], n_in, n->in_a, n->in_c); ::dexgg::count_launches(1);
     DEXGG_CUDA_OK(cudaMemsetAsync(n->tail_a, 0, 2 * n->tailw * sizeof(float), st));
     if (!gen) {
         DEXGG_CUDA_OK(cudaMemcpyAsync(n->tail_a, n->in_a + IN_BPS, n->n_tail * 4, cudaMemcpyDeviceToDevice, st));
@@ -191,22 +191,22 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
             const float* bias = part == 0 ? q[1] : q[13];
             const int rows = part == 0 ? INNER : HID, r0 = part == 0 ? 0 : INNER;
             float* wb = n->Wb + (size_t)(b * NCAT + r0) * IN_BPS;
-            pack_cols_kernel<<<nblk((int64_t)rows * IN_BPS), 256, 0, st>>>(wb, IN_BPS, 0, w, fin, L.bps_off, IN_BPS, rows, n->in_a);
-            fold_bias_kernel<<<nblk(rows, 8), 256, 0, st>>>(n->bb + b * NCAT + r0, bias, w, fin, L.bps_off, IN_BPS, rows, n->in_c);
+            pack_cols_kernel<<<nblk((int64_t)rows * IN_BPS), 256, 0, st>>>(wb, IN_BPS, 0, w, fin, L.bps_off, IN_BPS, rows, n->in_a); ::dexgg::count_launches(1);
+            fold_bias_kernel<<<nblk(rows, 8), 256, 0, st>>>(n->bb + b * NCAT + r0, bias, w, fin, L.bps_off, IN_BPS, rows, n->in_c); ::dexgg::count_launches(1);
             float* wt = B.Wt + (size_t)r0 * B.KT;
             int col = 0;
             if (L.x_off >= 0) {
-                pack_cols_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT, 0, w, fin, L.x_off, HID, rows, nullptr);
+                pack_cols_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT, 0, w, fin, L.x_off, HID, rows, nullptr); ::dexgg::count_launches(1);
                 col = HID;
             }
-            pack_cols_kernel<<<nblk((int64_t)rows * n->n_tail), 256, 0, st>>>(wt, B.KT, col, w, fin, L.tail_off, n->n_tail, rows, nullptr);
+            pack_cols_kernel<<<nblk((int64_t)rows * n->n_tail), 256, 0, st>>>(wt, B.KT, col, w, fin, L.tail_off, n->n_tail, rows, nullptr); ::dexgg::count_launches(1);
         }
-        bn_affine_kernel<<<nblk(INNER), 256, 0, st>>>(q[2], q[3], q[4], q[5], INNER, B.sc, B.sh);
-        fill_kernel<<<nblk(HID), 256, 0, st>>>(B.sc + INNER, 1.f, HID);
-        fill_kernel<<<nblk(HID), 256, 0, st>>>(B.sh + INNER, 0.f, HID);
+        bn_affine_kernel<<<nblk(INNER), 256, 0, st>>>(q[2], q[3], q[4], q[5], INNER, B.sc, B.sh); ::dexgg::count_launches(1);
+        fill_kernel<<<nblk(HID), 256, 0, st>>>(B.sc + INNER, 1.f, HID); ::dexgg::count_launches(1);
+        fill_kernel<<<nblk(HID), 256, 0, st>>>(B.sh + INNER, 0.f, HID); ::dexgg::count_launches(1);
         DEXGG_CUDA_OK(cudaMemcpyAsync(B.W2, q[6], (size_t)HID * INNER * 4, cudaMemcpyDeviceToDevice, st));
-        bn_affine_kernel<<<nblk(HID), 256, 0, st>>>(q[8], q[9], q[10], q[11], HID, n->tmp_a, n->tmp_c);
-        affine_bias_kernel<<<nblk(HID), 256, 0, st>>>(n->tmp_a, n->tmp_c, q[7], HID, B.sc2, B.sh2);
+        bn_affine_kernel<<<nblk(HID), 256, 0, st>>>(q[8], q[9], q[10], q[11], HID, n->tmp_a, n->tmp_c); ::dexgg::count_launches(1);
+        affine_bias_kernel<<<nblk(HID), 256, 0, st>>>(n->tmp_a, n->tmp_c, q[7], HID, B.sc2, B.sh2); ::dexgg::count_launches(1);
     }
     const float* const* h = P + 4 + 14 * n->n_blocks;
     if (gen) {  // rows: joint_conf (nJ) | rot6d (6) | transl (3)
@@ -392,7 +392,7 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
         TailDst d{{w.tail, w.XT0 + HID, nullptr}, {tw, ldx, 0}};
-        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(z + r0 * zD, zD, nullptr, 0, nullptr, 0, nullptr, nullptr, tw, mc, d);
+        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(z + r0 * zD, zD, nullptr, 0, nullptr, 0, nullptr, nullptr, tw, mc, d); ::dexgg::count_launches(1);
         if ((rc = run_block(net, 0, w.tail, tw, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
         if ((rc = run_block(net, 1, w.XT0, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT1, ldx, st))) return rc;
         LinearF32 h;
@@ -400,7 +400,7 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
         h.ep.bias = net->bh;
         if ((rc = linear_f32(h, st))) return rc;
         pose_finish_kernel<<<nblk(mc, 128), 128, 0, st>>>(w.H, 32, net->nJ, mc, z_offset, rot + r0 * 9, transl + r0 * 3,
-                                                         joint + r0 * net->nJ, rot6d ? rot6d + r0 * 6 : nullptr);
+                                                         joint + r0 * net->nJ, rot6d ? rot6d + r0 * 6 : nullptr); ::dexgg::count_launches(1);
     }
     DEXGG_LAUNCH_OK("generator_forward kernels");
     return DEXGG_OK;
@@ -424,7 +424,7 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
         TailDst d{{w.tail, w.XT0 + HID, w.XT1 + HID}, {tw, ldx, ldx}};
         pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(rot + r0 * 9, 9, transl + r0 * 3, 3, disc ? joint + r0 * nJ : nullptr,
-                                                       disc ? nJ : 0, net->tail_a, net->tail_c, tw, mc, d);
+                                                       disc ? nJ : 0, net->tail_a, net->tail_c, tw, mc, d); ::dexgg::count_launches(1);
         if ((rc = run_block(net, 0, w.tail, tw, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
         if ((rc = run_block(net, 1, w.XT0, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT1, ldx, st))) return rc;
         const float* X = w.XT1;
@@ -432,7 +432,7 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
             if ((rc = run_block(net, 2, w.XT1, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
             X = w.XT0;
         }
-        rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(X, ldx, net->Wh, net->bh, HID, mc, p + r0);
+        rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(X, ldx, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);
     }
     DEXGG_LAUNCH_OK("score forward kernels");
     return DEXGG_OK;

@@ -64,7 +64,7 @@ extern "C" int dexgg_rot6d_forward(const float* r6, int64_t M, float* rot, void*
     DEXGG_ARCH_OK();
     DEXGG_REQUIRE(M >= 0 && (M == 0 || (r6 && rot)), "rot6d_forward: bad arguments");
     if (M == 0) return DEXGG_OK;
-    rot6d_forward_kernel<<<(unsigned)((M + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(r6, M, rot);
+    rot6d_forward_kernel<<<(unsigned)((M + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(r6, M, rot); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("rot6d_forward_kernel");
     return DEXGG_OK;
 }
@@ -73,7 +73,7 @@ extern "C" int dexgg_rot6d_backward(const float* r6, const float* g_rot, int64_t
     DEXGG_ARCH_OK();
     DEXGG_REQUIRE(M >= 0 && (M == 0 || (r6 && g_rot && g_r6)), "rot6d_backward: bad arguments");
     if (M == 0) return DEXGG_OK;
-    rot6d_backward_kernel<<<(unsigned)((M + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(r6, g_rot, M, g_r6);
+    rot6d_backward_kernel<<<(unsigned)((M + 127) / 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(r6, g_rot, M, g_r6); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("rot6d_backward_kernel");
     return DEXGG_OK;
 }

@@ -1,0 +1,85 @@
+"""Batched grasp synthesis: point clouds -> BPS -> DexGenerator -> rot6d/offset -> DexEvaluator -> per-object top-k.
+
+The batched form of the reference's per-object loop (dexgangrasp_real_robot.py:131-162, dexgangrasp_offline.py:147-162):
+bps.encode -> generate_grasps(n) -> filter_grasps(thresh) -> first k rows.  Everything stays on the device between the
+stages; the encoding is used once per object (no np.tile); objects shard over ranks with no collective.
+"""
+import numpy as np
+import torch
+
+from . import _native
+from . import bps as bps_mod
+
+
+class GraspPipeline:
+    def __init__(self, gan, evaluator, basis=None, k=10, thresh=0.5, z_offset=0.025):
+        """gan: networks.DexGANGrasp, evaluator: networks.DexEvaluator (both on the same CUDA device, eval mode)."""
+        self.gan, self.eva = gan, evaluator
+        self.device = gan.device
+        if basis is None:
+            basis = np.load(bps_mod.BASIS_PATH)
+        self.basis = torch.as_tensor(np.asarray(basis), dtype=torch.float32).to(self.device).contiguous()
+        self.k, self.thresh, self.z_offset = int(k), float(thresh), float(z_offset)
+        self._ws = bps_mod._Workspace()
+        self._stage = {}
+        gan.eval()
+        evaluator.eval()
+
+    # ------------------------------------------------------------------ device-resident path
+    def encode(self, clouds):
+        """clouds [B,N,3] f32 cuda -> BPS distances [B,4096]"""
+        d, _ = bps_mod.bps_encode_device(self.basis, clouds, return_idx=False, ws=self._ws)
+        return d
+
+    def run_device(self, clouds, z, samples_per_object):
+        """clouds [B,N,3], z [B*S,latentD] on the device.  Returns a dict of device tensors:
+        idx [B,k] i32 (global row ids, -1 padded), count [B], score [B,k], rot_matrix [B,k,3,3], transl [B,k,3],
+        joint_conf [B,k,nJ] (rows beyond count are zero)."""
+        S = int(samples_per_object)
+        B = clouds.shape[0]
+        M = B * S
+        assert z.shape[0] == M
+        L = _native.lib()
+        dev = self.device
+        enc = self.encode(clouds)
+        rot, transl, joint, _ = self.gan.generator.native_forward(z, enc, self.z_offset, False)
+        p = self.eva.native_forward(enc, rot, transl)
+        k = min(self.k, S)
+        idx = torch.empty((B, k), dtype=torch.int32, device=dev)
+        cnt = torch.empty((B,), dtype=torch.int32, device=dev)
+        score = torch.empty((B, k), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _native.check(L.dexgg_filter_topk(p.data_ptr(), M, S, self.thresh, k, idx.data_ptr(), cnt.data_ptr(), None,
+                                              score.data_ptr(), _native.stream_ptr(dev)))
+        sel = idx.clamp_min(0).long().reshape(-1)
+        valid = (idx >= 0).reshape(-1, 1).float()
+        out = {
+            "idx": idx, "count": cnt, "score": score,
+            "rot_matrix": (rot.reshape(M, 9).index_select(0, sel) * valid).reshape(B, k, 3, 3),
+            "transl": (transl.index_select(0, sel) * valid).reshape(B, k, 3),
+            "joint_conf": (joint.index_select(0, sel) * valid).reshape(B, k, -1),
+            "bps": enc, "p": p,
+        }
+        return out
+
+    # ------------------------------------------------------------------ host-buffer path (the e2e number of bench.py)
+    def run_host(self, clouds_host, z_host, samples_per_object):
+        """clouds_host / z_host: pinned CPU tensors.  Copies them to the device, runs the path and reads the top-k result
+        back to the host (one packed [B,k,26+nJ... ] block + counts).  Returns (dict of CPU tensors, h2d bytes, d2h bytes)."""
+        dev = self.device
+        key = (tuple(clouds_host.shape), tuple(z_host.shape))
+        if key not in self._stage:
+            self._stage = {key: (torch.empty(clouds_host.shape, dtype=torch.float32, device=dev),
+                                 torch.empty(z_host.shape, dtype=torch.float32, device=dev))}
+        d_clouds, d_z = self._stage[key]
+        d_clouds.copy_(clouds_host, non_blocking=True)
+        d_z.copy_(z_host, non_blocking=True)
+        out = self.run_device(d_clouds, d_z, samples_per_object)
+        B, k = out["idx"].shape
+        packed = torch.cat([out["score"].reshape(B, k, 1), out["idx"].float().reshape(B, k, 1), out["rot_matrix"].reshape(B, k, 9),
+                            out["transl"], out["joint_conf"]], dim=2)
+        host = packed.cpu()  # synchronising D2H read of the result
+        cnt = out["count"].cpu()
+        h2d = clouds_host.numel() * 4 + z_host.numel() * 4
+        d2h = host.numel() * 4 + cnt.numel() * 4
+        return {"packed": host, "count": cnt}, h2d, d2h

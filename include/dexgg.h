@@ -39,6 +39,8 @@ int dexgg_version(void);
 const char* dexgg_last_error(void);
 /* 0 when the CURRENT device can run this library (compute capability 10.x), else DEXGG_E_ARCH / DEXGG_E_CUDA. */
 int dexgg_device_check(void);
+/* Number of CUDA kernels this library has launched since it was loaded (bench.py reports the per-step difference). */
+unsigned long long dexgg_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Stage 1 — Basis Point Set encoding.
