@@ -41,6 +41,21 @@ struct LinearF32 {
 
 int linear_f32(const LinearF32& p, cudaStream_t st);  // linear_simt.cu
 
+struct LinearB16 {  // bf16 operands (K-major, row pitch a multiple of 16 bytes), fp32 accumulation on the tensor cores
+    const void* A = nullptr;  // bf16 [M,K]
+    int64_t lda = 0;
+    const void* W = nullptr;  // bf16 [N,K]
+    int64_t ldw = 0;
+    int M = 0, N = 0, K = 0;
+    Epilogue ep;                       // fp32 side inputs; ep.residual is ignored
+    const void* residual16 = nullptr;  // bf16 [M, ldr]
+    int64_t ldr = 0;
+    void* C16 = nullptr;   // bf16 output [M, ldc] and / or
+    float* C32 = nullptr;  // fp32 output [M, ldc]
+    int64_t ldc = 0;
+};
+int linear_bf16(const LinearB16& p, cudaStream_t st);  // linear_umma.cu
+
 #define DEXGG_LRELU_SLOPE 0.2f
 
 __device__ __forceinline__ float apply_epilogue(const Epilogue& ep, float v, int m, int n) {
