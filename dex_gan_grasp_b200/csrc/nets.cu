@@ -14,6 +14,8 @@
 //   heads Wh [nh,512], bh [nh]
 // "tail" = the per-row inputs that are not BPS: z (generator), bn1(rot9,transl3) (evaluator), bn1(rot9,transl3,joints)
 // (discriminator), zero-padded to tailw = 16 or 32 columns.
+#include <cuda_bf16.h>
+
 #include "linear.cuh"
 
 #include <new>
@@ -137,6 +139,95 @@ __global__ void rowdot_sigmoid_kernel(const float* X, int64_t ldx, const float* 
     if (lane == 0) p[m] = 1.f / (1.f + expf(-(s + b[0])));
 }
 
+// ---------------------------------------------------------------- bf16 tensor-core mode helpers
+// A value x is carried as two bf16 numbers hi = bf16(x), lo = bf16(x - hi); with operands laid out along K as
+// A' = [a_hi | a_lo | a_hi] and W' = [w_hi | w_hi | w_lo] one ordinary bf16 GEMM accumulates a_hi*w_hi + a_lo*w_hi + a_hi*w_lo,
+// i.e. the product to ~2^-17 relative.  Used for the inputs that are NOT hidden activations (BPS encoding, z, pose).
+__device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+    hi = __float2bfloat16_rn(x);
+    lo = __float2bfloat16_rn(x - __bfloat162float(hi));
+}
+// dst[r, c_hi1 + j] = dst[r, c_hi2 + j] = hi(src[r, scol0 + j]);  dst[r, c_lo + j] = lo(...)
+__global__ void pack_split_cols_kernel(__nv_bfloat16* dst, int64_t ldd, int c_hi1, int c_hi2, int c_lo, const float* src,
+                                       int64_t lds, int scol0, int ncols, int nrows) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)ncols * nrows) return;
+    const int r = (int)(i / ncols), j = (int)(i % ncols);
+    __nv_bfloat16 hi, lo;
+    split_bf16(src[r * lds + scol0 + j], hi, lo);
+    dst[r * ldd + c_hi1 + j] = hi;
+    dst[r * ldd + c_hi2 + j] = hi;
+    dst[r * ldd + c_lo + j] = lo;
+}
+__global__ void pack_cols_bf16_kernel(__nv_bfloat16* dst, int64_t ldd, int dcol0, const float* src, int64_t lds, int scol0,
+                                      int ncols, int nrows) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)ncols * nrows) return;
+    const int r = (int)(i / ncols), j = (int)(i % ncols);
+    dst[r * ldd + dcol0 + j] = __float2bfloat16_rn(src[r * lds + scol0 + j]);
+}
+// out[o, :] = [hi | lo | hi] of a[k]*bps[o,k] + c[k]   (input BatchNorm applied in fp32 before the split)
+__global__ void bps_bn_split_kernel(const float* __restrict__ bps, const float* __restrict__ a, const float* __restrict__ c,
+                                    __nv_bfloat16* __restrict__ out, int64_t n_obj) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_obj * IN_BPS) return;
+    const int64_t o = i / IN_BPS;
+    const int k = (int)(i % IN_BPS);
+    __nv_bfloat16 hi, lo;
+    split_bf16(fmaf(a[k], bps[i], c[k]), hi, lo);
+    __nv_bfloat16* row = out + o * (3 * IN_BPS);
+    row[k] = hi;
+    row[IN_BPS + k] = lo;
+    row[2 * IN_BPS + k] = hi;
+}
+struct TailDst16 {
+    __nv_bfloat16* p[3];
+    int64_t ld[3];
+};
+// like pack_tail_kernel, output [hi (width) | lo (width) | hi (width)] in bf16
+__global__ void pack_tail16_kernel(const float* s0, int n0, const float* s1, int n1, const float* s2, int n2, const float* a,
+                                   const float* c, int width, int64_t M, TailDst16 d) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M * width) return;
+    const int64_t m = i / width;
+    const int j = (int)(i % width);
+    float v = 0.f;
+    if (j < n0) v = s0[m * n0 + j];
+    else if (j < n0 + n1) v = s1[m * n1 + (j - n0)];
+    else if (j < n0 + n1 + n2) v = s2[m * n2 + (j - n0 - n1)];
+    if (a && j < n0 + n1 + n2) v = fmaf(a[j], v, c[j]);
+    __nv_bfloat16 hi, lo;
+    split_bf16(v, hi, lo);
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+        if (d.p[q]) {
+            __nv_bfloat16* row = d.p[q] + m * d.ld[q];
+            row[j] = hi;
+            row[width + j] = lo;
+            row[2 * width + j] = hi;
+        }
+}
+__global__ void rowdot_sigmoid_bf16_kernel(const __nv_bfloat16* X, int64_t ldx, const float* w, const float* b, int K, int64_t M,
+                                           float* p) {
+    const int64_t m = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (m >= M) return;
+    const __nv_bfloat16* x = X + m * ldx;
+    float s = 0.f;
+    for (int k = lane * 8; k < K; k += 256) {
+        const uint4 u = *reinterpret_cast<const uint4*>(x + k);
+        const uint32_t q[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+            s = fmaf(__uint_as_float(q[h] << 16), w[k + 2 * h], s);
+            s = fmaf(__uint_as_float(q[h] & 0xffff0000u), w[k + 2 * h + 1], s);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) p[m] = 1.f / (1.f + expf(-(s + b[0])));
+}
+
 }  // namespace dexgg
 
 using namespace dexgg;
@@ -145,12 +236,19 @@ using namespace dexgg;
 struct BlockPack {
     float *Wt, *sc, *sh, *W2, *sc2, *sh2;
     int KT, has_x;
+    // bf16 tensor-core mode: Wt16 [768, KT16] = [X (512) | tail hi | tail hi | tail lo], W2_16 [512,256]
+    __nv_bfloat16 *Wt16, *W2_16;
+    int KT16;
 };
 struct dexgg_net {
     int kind, precision, latentD, nJ;
     int n_blocks, n_tail, tailw, nbase, nh, n_params;
     float *Wb, *bb, *in_a, *in_c, *tail_a, *tail_c, *Wh, *bh, *tmp_a, *tmp_c;
     BlockPack blk[3];
+    // bf16 mode: Wb16 [nbase, 3*4096] = [hi | hi | lo] of the RAW BPS columns (BatchNorm applied to the input instead),
+    // bb_raw [nbase] raw biases, Wh16 [32,512] generator heads
+    __nv_bfloat16 *Wb16, *Wh16;
+    float* bb_raw;
     void* arena;
     size_t arena_bytes;
 };
@@ -207,6 +305,22 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
         DEXGG_CUDA_OK(cudaMemcpyAsync(B.W2, q[6], (size_t)HID * INNER * 4, cudaMemcpyDeviceToDevice, st));
         bn_affine_kernel<<<nblk(HID), 256, 0, st>>>(q[8], q[9], q[10], q[11], HID, n->tmp_a, n->tmp_c); ::dexgg::count_launches(1);
         affine_bias_kernel<<<nblk(HID), 256, 0, st>>>(n->tmp_a, n->tmp_c, q[7], HID, B.sc2, B.sh2); ::dexgg::count_launches(1);
+        if (n->precision == DEXGG_PRECISION_BF16) {
+            const int tw = n->tailw, xo = B.has_x ? HID : 0;
+            DEXGG_CUDA_OK(cudaMemsetAsync(B.Wt16, 0, (size_t)NCAT * B.KT16 * 2, st));
+            for (int part = 0; part < 2; ++part) {
+                const float* w = part == 0 ? q[0] : q[12];
+                const float* bias = part == 0 ? q[1] : q[13];
+                const int rows = part == 0 ? INNER : HID, r0 = part == 0 ? 0 : INNER;
+                __nv_bfloat16* wb = n->Wb16 + (size_t)(b * NCAT + r0) * (3 * IN_BPS);
+                pack_split_cols_kernel<<<nblk((int64_t)rows * IN_BPS), 256, 0, st>>>(wb, 3 * IN_BPS, 0, IN_BPS, 2 * IN_BPS, w, fin, L.bps_off, IN_BPS, rows); ::dexgg::count_launches(1);
+                DEXGG_CUDA_OK(cudaMemcpyAsync(n->bb_raw + b * NCAT + r0, bias, rows * 4, cudaMemcpyDeviceToDevice, st));
+                __nv_bfloat16* wt = B.Wt16 + (size_t)r0 * B.KT16;
+                if (B.has_x) { pack_cols_bf16_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT16, 0, w, fin, L.x_off, HID, rows); ::dexgg::count_launches(1); }
+                pack_split_cols_kernel<<<nblk((int64_t)rows * n->n_tail), 256, 0, st>>>(wt, B.KT16, xo, xo + tw, xo + 2 * tw, w, fin, L.tail_off, n->n_tail, rows); ::dexgg::count_launches(1);
+            }
+            pack_cols_bf16_kernel<<<nblk((int64_t)HID * INNER), 256, 0, st>>>(B.W2_16, INNER, 0, q[6], INNER, 0, INNER, HID); ::dexgg::count_launches(1);
+        }
     }
     const float* const* h = P + 4 + 14 * n->n_blocks;
     if (gen) {  // rows: joint_conf (nJ) | rot6d (6) | transl (3)
@@ -220,6 +334,10 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
     } else {
         DEXGG_CUDA_OK(cudaMemcpyAsync(n->Wh, h[0], HID * 4, cudaMemcpyDeviceToDevice, st));
         DEXGG_CUDA_OK(cudaMemcpyAsync(n->bh, h[1], 4, cudaMemcpyDeviceToDevice, st));
+    }
+    if (gen && n->precision == DEXGG_PRECISION_BF16) {
+        DEXGG_CUDA_OK(cudaMemsetAsync(n->Wh16, 0, (size_t)32 * HID * 2, st));
+        pack_cols_bf16_kernel<<<nblk((int64_t)n->nh * HID), 256, 0, st>>>(n->Wh16, HID, 0, n->Wh, HID, 0, HID, n->nh); ::dexgg::count_launches(1);
     }
     DEXGG_LAUNCH_OK("net packing kernels");
     return DEXGG_OK;
@@ -257,24 +375,49 @@ void carve_net(dexgg_net* n, Carver& c) {
         B.W2 = c.take<float>((size_t)HID * INNER);
         B.sc2 = c.take<float>(HID);
         B.sh2 = c.take<float>(HID);
+        B.KT16 = (B.has_x ? HID : 0) + 3 * n->tailw;
+        B.Wt16 = nullptr;
+        B.W2_16 = nullptr;
+        if (n->precision == DEXGG_PRECISION_BF16) {
+            B.Wt16 = c.take<__nv_bfloat16>((size_t)NCAT * B.KT16);
+            B.W2_16 = c.take<__nv_bfloat16>((size_t)HID * INNER);
+        }
+    }
+    n->Wb16 = nullptr; n->Wh16 = nullptr; n->bb_raw = nullptr;
+    if (n->precision == DEXGG_PRECISION_BF16) {
+        n->Wb16 = c.take<__nv_bfloat16>((size_t)n->nbase * 3 * IN_BPS);
+        n->Wh16 = c.take<__nv_bfloat16>((size_t)32 * HID);
+        n->bb_raw = c.take<float>(n->nbase);
     }
 }
 
-// workspace of one forward call
+// workspace of one forward call.  Activations are fp32 (CUDA-core mode) or bf16 (tensor-core mode); `es` is the element
+// size, `tw` the tail width in elements (tailw, or 3*tailw for the hi|lo|hi split), ldx = 512 + tw.
 struct FwdWs {
-    float *base, *tail, *T, *XT0, *XT1, *H;
+    float *base, *H;
+    char *tail, *T, *XT0, *XT1;
+    __nv_bfloat16* Ab16;  // bf16 mode: [n_obj, 3*4096] split of bn(bps)
     int64_t mc;
+    int es, tw, ldx;
 };
 size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w) {
     Carver c{static_cast<char*>(ws)};
-    const int64_t mc = M < CHUNK_ROWS ? M : CHUNK_ROWS;
+    const bool b16 = n->precision == DEXGG_PRECISION_BF16;
+    // bf16: one chunk = 128 rows per SM, so every layer's tile count is a multiple of the SM count and the chunk's
+    // activations (~60 MB) stay resident in the 126 MB L2 between layers
+    const int64_t chunk = b16 ? (int64_t)sm_count() * 128 : CHUNK_ROWS;
+    const int64_t mc = M < chunk ? M : chunk;
     w.mc = mc;
+    w.es = b16 ? 2 : 4;
+    w.tw = b16 ? 3 * n->tailw : n->tailw;
+    w.ldx = HID + w.tw;
     w.base = c.take<float>((size_t)n_obj * n->nbase);
-    w.tail = c.take<float>((size_t)mc * n->tailw);
-    w.T = c.take<float>((size_t)mc * NCAT);
-    w.XT0 = c.take<float>((size_t)mc * (HID + n->tailw));
-    w.XT1 = c.take<float>((size_t)mc * (HID + n->tailw));
     w.H = c.take<float>((size_t)mc * 32);
+    w.tail = c.take<char>((size_t)mc * w.tw * w.es);
+    w.T = c.take<char>((size_t)mc * NCAT * w.es);
+    w.XT0 = c.take<char>((size_t)mc * w.ldx * w.es);
+    w.XT1 = c.take<char>((size_t)mc * w.ldx * w.es);
+    w.Ab16 = b16 ? c.take<__nv_bfloat16>((size_t)n_obj * 3 * IN_BPS) : nullptr;
     return c.used;
 }
 
@@ -283,7 +426,7 @@ int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int6
     DEXGG_REQUIRE(n && n->kind == kind, "forward: wrong or null net handle");
     DEXGG_REQUIRE(n_obj >= 0 && rows_per_obj >= 1 && M == n_obj * rows_per_obj, "forward: M (%lld) must equal n_obj*rows_per_obj (%lld*%lld)",
                   (long long)M, (long long)n_obj, (long long)rows_per_obj);
-    DEXGG_REQUIRE(rows_per_obj < (1ll << 31) && M < (1ll << 40), "forward: sizes too large");
+    DEXGG_REQUIRE(rows_per_obj < (1ll << 31) && M < (1ll << 40) && n_obj < (1ll << 31), "forward: sizes too large");
     DEXGG_REQUIRE(M == 0 || bps, "forward: null bps");
     FwdWs w;
     const size_t need = carve_ws(n, M, n_obj, nullptr, w);
@@ -294,28 +437,66 @@ int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int6
     return DEXGG_OK;
 }
 
-// base[n_obj, nbase] = bps · Wbᵀ + bb    (once per object; for row-wise inputs n_obj == M)
-int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, float* base, cudaStream_t st) {
+// base[n_obj, nbase] = bn(bps) · W_bpsᵀ + bias    (once per object; for row-wise inputs n_obj == M)
+int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, const FwdWs& w, cudaStream_t st) {
+    if (n->precision == DEXGG_PRECISION_BF16) {
+        bps_bn_split_kernel<<<nblk(n_obj * IN_BPS), 256, 0, st>>>(bps, n->in_a, n->in_c, w.Ab16, n_obj); ::dexgg::count_launches(1);
+        LinearB16 q;
+        q.A = w.Ab16; q.lda = 3 * IN_BPS; q.W = n->Wb16; q.ldw = 3 * IN_BPS;
+        q.M = (int)n_obj; q.N = n->nbase; q.K = 3 * IN_BPS; q.C32 = w.base; q.ldc = n->nbase;
+        q.ep.bias = n->bb_raw;
+        return linear_bf16(q, st);
+    }
     LinearF32 p;
     p.A = bps; p.lda = IN_BPS; p.W = n->Wb; p.ldw = IN_BPS;
-    p.M = (int)n_obj; p.N = n->nbase; p.K = IN_BPS; p.C = base; p.ldc = n->nbase;
+    p.M = (int)n_obj; p.N = n->nbase; p.K = IN_BPS; p.C = w.base; p.ldc = n->nbase;
     p.ep.bias = n->bb;
     return linear_f32(p, st);
 }
 
+// tail columns (z / normalised pose) of the chunk into up to three activation buffers
+void pack_tail(const dexgg_net* n, const FwdWs& w, const float* s0, int n0, const float* s1, int n1, const float* s2, int n2,
+               bool affine, int64_t mc, char* d0, int64_t ld0, char* d1, int64_t ld1, char* d2, int64_t ld2, cudaStream_t st) {
+    const float* a = affine ? n->tail_a : nullptr;
+    const float* c = affine ? n->tail_c : nullptr;
+    const int tw = n->tailw;
+    if (n->precision == DEXGG_PRECISION_BF16) {
+        TailDst16 d{{reinterpret_cast<__nv_bfloat16*>(d0), reinterpret_cast<__nv_bfloat16*>(d1), reinterpret_cast<__nv_bfloat16*>(d2)}, {ld0, ld1, ld2}};
+        pack_tail16_kernel<<<nblk(mc * tw), 256, 0, st>>>(s0, n0, s1, n1, s2, n2, a, c, tw, mc, d); ::dexgg::count_launches(1);
+    } else {
+        TailDst d{{reinterpret_cast<float*>(d0), reinterpret_cast<float*>(d1), reinterpret_cast<float*>(d2)}, {ld0, ld1, ld2}};
+        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(s0, n0, s1, n1, s2, n2, a, c, tw, mc, d); ::dexgg::count_launches(1);
+    }
+}
+
 // One ResBlock on a chunk: T = lrelu(sc*(A·Wtᵀ + base) + sh);  Xout = lrelu(T[:,256:] + sc2*(T[:,:256]·W2ᵀ) + sh2)
-int run_block(const dexgg_net* n, int b, const float* A, int64_t lda, const float* base, int rows_per_obj, int64_t row0,
-              int64_t mc, float* T, float* Xout, int64_t ldx, cudaStream_t st) {
+int run_block(const dexgg_net* n, int b, const FwdWs& w, const char* A, int64_t lda, int rows_per_obj, int64_t row0, int64_t mc,
+              char* Xout, cudaStream_t st) {
     const BlockPack& B = n->blk[b];
+    Epilogue e1;
+    e1.base = w.base + b * NCAT; e1.ldbase = n->nbase; e1.rows_per_obj = rows_per_obj; e1.row0 = row0;
+    e1.scale = B.sc; e1.shift = B.sh; e1.act = 1;
+    Epilogue e2;
+    e2.scale = B.sc2; e2.shift = B.sh2; e2.act = 1;
+    if (n->precision == DEXGG_PRECISION_BF16) {
+        LinearB16 p;
+        p.A = A; p.lda = lda; p.W = B.Wt16; p.ldw = B.KT16; p.M = (int)mc; p.N = NCAT; p.K = B.KT16; p.C16 = w.T; p.ldc = NCAT; p.ep = e1;
+        int rc = linear_bf16(p, st);
+        if (rc) return rc;
+        LinearB16 q;
+        q.A = w.T; q.lda = NCAT; q.W = B.W2_16; q.ldw = INNER; q.M = (int)mc; q.N = HID; q.K = INNER; q.C16 = Xout; q.ldc = w.ldx; q.ep = e2;
+        q.residual16 = w.T + INNER * 2; q.ldr = NCAT;
+        return linear_bf16(q, st);
+    }
     LinearF32 p;
-    p.A = A; p.lda = lda; p.W = B.Wt; p.ldw = B.KT; p.M = (int)mc; p.N = NCAT; p.K = B.KT; p.C = T; p.ldc = NCAT;
-    p.ep.base = base + b * NCAT; p.ep.ldbase = n->nbase; p.ep.rows_per_obj = rows_per_obj; p.ep.row0 = row0;
-    p.ep.scale = B.sc; p.ep.shift = B.sh; p.ep.act = 1;
+    p.A = reinterpret_cast<const float*>(A); p.lda = lda; p.W = B.Wt; p.ldw = B.KT; p.M = (int)mc; p.N = NCAT; p.K = B.KT;
+    p.C = reinterpret_cast<float*>(w.T); p.ldc = NCAT; p.ep = e1;
     int rc = linear_f32(p, st);
     if (rc) return rc;
     LinearF32 q;
-    q.A = T; q.lda = NCAT; q.W = B.W2; q.ldw = INNER; q.M = (int)mc; q.N = HID; q.K = INNER; q.C = Xout; q.ldc = ldx;
-    q.ep.scale = B.sc2; q.ep.shift = B.sh2; q.ep.residual = T + INNER; q.ep.ldr = NCAT; q.ep.act = 1;
+    q.A = reinterpret_cast<const float*>(w.T); q.lda = NCAT; q.W = B.W2; q.ldw = INNER; q.M = (int)mc; q.N = HID; q.K = INNER;
+    q.C = reinterpret_cast<float*>(Xout); q.ldc = w.ldx; q.ep = e2;
+    q.ep.residual = reinterpret_cast<const float*>(w.T) + INNER; q.ep.ldr = NCAT;
     return linear_f32(q, st);
 }
 }  // namespace
@@ -326,7 +507,7 @@ extern "C" int dexgg_net_create(int kind, const float* const* params, int n_para
     DEXGG_REQUIRE(out && params, "net_create: null argument");
     DEXGG_REQUIRE(kind >= DEXGG_NET_GENERATOR && kind <= DEXGG_NET_EVALUATOR, "net_create: unknown kind %d", kind);
     DEXGG_REQUIRE(n_params == n_expected(kind), "net_create: kind %d takes %d parameter tensors, got %d", kind, n_expected(kind), n_params);
-    DEXGG_REQUIRE(precision == DEXGG_PRECISION_FP32, "net_create: unsupported precision %d", precision);
+    DEXGG_REQUIRE(precision == DEXGG_PRECISION_FP32 || precision == DEXGG_PRECISION_BF16, "net_create: unsupported precision %d", precision);
     DEXGG_REQUIRE(latent_dim >= 1 && latent_dim <= 16 && n_joints >= 1 && n_joints <= 20, "net_create: latent_dim/n_joints out of range");
     for (int i = 0; i < n_params; ++i) DEXGG_REQUIRE(params[i], "net_create: parameter %d is null", i);
     dexgg_net* n = new (std::nothrow) dexgg_net();
@@ -387,18 +568,26 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     FwdWs w;
     carve_ws(net, M, n_obj, workspace, w);
-    if ((rc = compute_base(net, bps, n_obj, w.base, st))) return rc;
-    const int tw = net->tailw, zD = net->latentD, ldx = HID + tw;
+    if ((rc = compute_base(net, bps, n_obj, w, st))) return rc;
+    const int zD = net->latentD;
+    const bool b16 = net->precision == DEXGG_PRECISION_BF16;
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
-        TailDst d{{w.tail, w.XT0 + HID, nullptr}, {tw, ldx, 0}};
-        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(z + r0 * zD, zD, nullptr, 0, nullptr, 0, nullptr, nullptr, tw, mc, d); ::dexgg::count_launches(1);
-        if ((rc = run_block(net, 0, w.tail, tw, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
-        if ((rc = run_block(net, 1, w.XT0, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT1, ldx, st))) return rc;
-        LinearF32 h;
-        h.A = w.XT1; h.lda = ldx; h.W = net->Wh; h.ldw = HID; h.M = (int)mc; h.N = net->nh; h.K = HID; h.C = w.H; h.ldc = 32;
-        h.ep.bias = net->bh;
-        if ((rc = linear_f32(h, st))) return rc;
+        pack_tail(net, w, z + r0 * zD, zD, nullptr, 0, nullptr, 0, false, mc, w.tail, w.tw, w.XT0 + HID * w.es, w.ldx, nullptr, 0, st);
+        if ((rc = run_block(net, 0, w, w.tail, w.tw, (int)rows_per_obj, r0, mc, w.XT0, st))) return rc;
+        if ((rc = run_block(net, 1, w, w.XT0, w.ldx, (int)rows_per_obj, r0, mc, w.XT1, st))) return rc;
+        if (b16) {
+            LinearB16 h;
+            h.A = w.XT1; h.lda = w.ldx; h.W = net->Wh16; h.ldw = HID; h.M = (int)mc; h.N = net->nh; h.K = HID; h.C32 = w.H; h.ldc = 32;
+            h.ep.bias = net->bh;
+            if ((rc = linear_bf16(h, st))) return rc;
+        } else {
+            LinearF32 h;
+            h.A = reinterpret_cast<const float*>(w.XT1); h.lda = w.ldx; h.W = net->Wh; h.ldw = HID; h.M = (int)mc; h.N = net->nh;
+            h.K = HID; h.C = w.H; h.ldc = 32;
+            h.ep.bias = net->bh;
+            if ((rc = linear_f32(h, st))) return rc;
+        }
         pose_finish_kernel<<<nblk(mc, 128), 128, 0, st>>>(w.H, 32, net->nJ, mc, z_offset, rot + r0 * 9, transl + r0 * 3,
                                                          joint + r0 * net->nJ, rot6d ? rot6d + r0 * 6 : nullptr); ::dexgg::count_launches(1);
     }
@@ -417,22 +606,26 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     FwdWs w;
     carve_ws(net, M, n_obj, workspace, w);
-    if ((rc = compute_base(net, bps, n_obj, w.base, st))) return rc;
-    const int tw = net->tailw, ldx = HID + tw, nJ = net->nJ;
+    if ((rc = compute_base(net, bps, n_obj, w, st))) return rc;
+    const int nJ = net->nJ;
     const bool disc = kind == DEXGG_NET_DISCRIMINATOR;
+    const bool b16 = net->precision == DEXGG_PRECISION_BF16;
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
-        TailDst d{{w.tail, w.XT0 + HID, w.XT1 + HID}, {tw, ldx, ldx}};
-        pack_tail_kernel<<<nblk(mc * tw), 256, 0, st>>>(rot + r0 * 9, 9, transl + r0 * 3, 3, disc ? joint + r0 * nJ : nullptr,
-                                                       disc ? nJ : 0, net->tail_a, net->tail_c, tw, mc, d); ::dexgg::count_launches(1);
-        if ((rc = run_block(net, 0, w.tail, tw, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
-        if ((rc = run_block(net, 1, w.XT0, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT1, ldx, st))) return rc;
-        const float* X = w.XT1;
+        pack_tail(net, w, rot + r0 * 9, 9, transl + r0 * 3, 3, disc ? joint + r0 * nJ : nullptr, disc ? nJ : 0, true, mc, w.tail, w.tw,
+                  w.XT0 + HID * w.es, w.ldx, w.XT1 + HID * w.es, w.ldx, st);
+        if ((rc = run_block(net, 0, w, w.tail, w.tw, (int)rows_per_obj, r0, mc, w.XT0, st))) return rc;
+        if ((rc = run_block(net, 1, w, w.XT0, w.ldx, (int)rows_per_obj, r0, mc, w.XT1, st))) return rc;
+        const char* X = w.XT1;
         if (!disc) {
-            if ((rc = run_block(net, 2, w.XT1, ldx, w.base, (int)rows_per_obj, r0, mc, w.T, w.XT0, ldx, st))) return rc;
+            if ((rc = run_block(net, 2, w, w.XT1, w.ldx, (int)rows_per_obj, r0, mc, w.XT0, st))) return rc;
             X = w.XT0;
         }
-        rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(X, ldx, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);
+        if (b16) {
+            rowdot_sigmoid_bf16_kernel<<<nblk(mc, 8), 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(X), w.ldx, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);
+        } else {
+            rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(reinterpret_cast<const float*>(X), w.ldx, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);
+        }
     }
     DEXGG_LAUNCH_OK("score forward kernels");
     return DEXGG_OK;

@@ -224,3 +224,76 @@ def test_checkpoint_layout_roundtrip(model, tmp_path):
     m2.load_dexevaluator(3)
     for a, b in zip(m.DexGANGrasp.state_dict().values(), m2.DexGANGrasp.state_dict().values()):
         assert torch.equal(a, b)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# bf16 tensor-core mode (tcgen05): hidden activations and weights are bf16, accumulation fp32; BPS / z / pose inputs are
+# carried as hi+lo bf16 pairs.  Stated tolerance (BASELINE.json north_star "bf16 mode ... within a stated score tolerance"):
+#   evaluator / discriminator scores within BF16_SCORE_TOL of the reference fp32 scores, generator outputs within
+#   BF16_POSE_TOL, and the filtered grasp set identical except rows whose fp32 score lies within BF16_SCORE_TOL of thresh.
+BF16_SCORE_TOL = 1e-2
+BF16_POSE_TOL = 1e-2
+
+
+@pytest.fixture(scope="module")
+def model_bf16():
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    m = DexGanGrasp(dict(CFG, precision="bf16"))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    m.DexGANGrasp.eval()
+    m.DexEvaluator.eval()
+    return m
+
+
+def test_bf16_mode_rowwise_vs_reference_golden(model_bf16, eval_batch, nets_golden):
+    m = model_bf16
+    bps = torch.from_numpy(eval_batch["bps_object"]).cuda()
+    z = torch.from_numpy(nets_golden["A/z"]).cuda()
+    rot, transl, joint, r6 = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, True)
+    d = {"rot_6D": md(r6, nets_golden["A/rot_6D"]), "transl": md(transl, nets_golden["A/transl"]),
+         "joint": md(joint, nets_golden["A/joint_conf"])}
+    p = m.DexEvaluator({"bps_object": bps, "rot_matrix": torch.from_numpy(nets_golden["A/rot_matrix"]),
+                        "transl": torch.from_numpy(nets_golden["A/transl"])})
+    real = {k: torch.from_numpy(eval_batch[k]) for k in ("bps_object", "rot_matrix", "transl", "joint_conf")}
+    d["p_eva"] = md(p, nets_golden["A/p_eva"])
+    d["p_disc_real"] = md(m.DexGANGrasp.discriminator(real), nets_golden["A/p_disc_real"])
+    print("bf16 vs reference fp32 (row-wise):", d)
+    assert d["rot_6D"] < BF16_POSE_TOL and d["transl"] < BF16_POSE_TOL and d["joint"] < BF16_POSE_TOL
+    assert d["p_eva"] < BF16_SCORE_TOL and d["p_disc_real"] < BF16_SCORE_TOL
+
+
+def test_bf16_mode_same_filtered_set(model_bf16, nets_golden):
+    m = model_bf16
+    z = torch.from_numpy(nets_golden["B/z"]).cuda()
+    bps = torch.from_numpy(nets_golden["B/bps"]).cuda()
+    rot, transl, joint, _ = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
+    assert md(transl, nets_golden["B/transl"]) < BF16_POSE_TOL and md(joint, nets_golden["B/joint_conf"]) < BF16_POSE_TOL
+    grasps = {"rot_matrix": nets_golden["B/rot_matrix"].copy(), "transl": nets_golden["B/transl"].copy(),
+              "joint_conf": nets_golden["B/joint_conf"].copy(), "z": nets_golden["B/z"].copy()}
+    p = m.evaluate_grasps(nets_golden["B/bps"], dict(grasps))
+    pg = nets_golden["B/p_eva"]
+    print("bf16 scores vs reference fp32 (shared BPS): max |dp| =", float(np.max(np.abs(p - pg))))
+    assert np.max(np.abs(p - pg)) < BF16_SCORE_TOL
+    thr = float(nets_golden["B/thresh_med"])
+    f = m.filter_grasps(nets_golden["B/bps"], grasps, thresh=thr)
+    kept = {int(np.where((nets_golden["B/z"] == row).all(1))[0][0]) for row in f["z"]}
+    sure_in = {i for i in range(len(pg)) if pg[i] > thr + BF16_SCORE_TOL}
+    sure_out = {i for i in range(len(pg)) if pg[i] < thr - BF16_SCORE_TOL}
+    assert sure_in <= kept and not (kept & sure_out)
+
+
+def test_bf16_mode_many_objects_vs_fp32_mode(model, model_bf16, bps_golden):
+    names = list(bps_golden["names"])
+    bps = torch.from_numpy(np.concatenate([bps_golden[f"{n}/bps"] for n in names]))
+    S = 3000  # 21000 rows: more than one 148x128-row chunk
+    z = synth.synth_latents(7 * S, 5, seed=31)
+    out32 = model.DexGANGrasp.generator.native_forward(z, bps, 0.025, True)
+    out16 = model_bf16.DexGANGrasp.generator.native_forward(z, bps, 0.025, True)
+    assert md(out16[3], out32[3]) < BF16_POSE_TOL and md(out16[1], out32[1]) < BF16_POSE_TOL and md(out16[2], out32[2]) < BF16_POSE_TOL
+    p32 = model.DexEvaluator.native_forward(bps, out32[0], out32[1])
+    p16 = model_bf16.DexEvaluator.native_forward(bps, out32[0], out32[1])
+    d32 = model.DexGANGrasp.discriminator.native_forward(bps, out32[0], out32[1], out32[2])
+    d16 = model_bf16.DexGANGrasp.discriminator.native_forward(bps, out32[0], out32[1], out32[2])
+    print("bf16 vs fp32 mode: max |dp_eva| =", md(p16, p32), " max |dp_disc| =", md(d16, d32), " r6", md(out16[3], out32[3]))
+    assert md(p16, p32) < BF16_SCORE_TOL and md(d16, d32) < BF16_SCORE_TOL
