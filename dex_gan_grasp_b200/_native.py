@@ -40,6 +40,17 @@ SIGNATURES = {
     "dexgg_f32_to_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_rot6d_forward": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
     "dexgg_rot6d_backward": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "dexgg_col_sum": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),
+    "dexgg_col_centered_sumsq": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_void_p]),
+    "dexgg_bn_finalize": (c_int, [c_void_p, c_int, c_float, c_int, c_float, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dexgg_bn_apply": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int,
+                               c_void_p, c_int64, c_void_p]),
+    "dexgg_lrelu_backward": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p, c_int64, c_void_p]),
+    "dexgg_bn_backward_reduce": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p,
+                                         c_void_p]),
+    "dexgg_bn_backward_apply": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                        c_float, c_int64, c_int, c_void_p, c_int64, c_void_p]),
+    "dexgg_adam_step": (c_int, [c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_int, c_void_p]),
     "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
 }
 

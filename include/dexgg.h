@@ -156,6 +156,34 @@ int dexgg_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int
 int dexgg_rot6d_forward(const float* r6, int64_t M, float* rot, void* stream);
 int dexgg_rot6d_backward(const float* r6, const float* g_rot, int64_t M, float* g_r6, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Training-step building blocks (DexGanGrasp.update_dexgangrasp / update_dexevaluator, models/dexgangrasp.py:739-823).
+ * Linear forward / dgrad / wgrad are dexgg_linear_f32 (trans flags); below are train-mode BatchNorm1d, LeakyReLU backward,
+ * bias gradients and Adam.  Row-major fp32 [M,N] activations with explicit row pitches.
+ *   BatchNorm forward (nn.BatchNorm1d in training mode, networks.py:33,36,71,117,289):
+ *     zero sum; dexgg_col_sum(x -> sum); [allreduce sum over ranks]; dexgg_bn_finalize(pass 0: mean = sum / count);
+ *     zero sumsq; dexgg_col_centered_sumsq(x, mean -> sumsq); [allreduce]; dexgg_bn_finalize(pass 1: invstd, running stats
+ *     with momentum and the unbiased variance); dexgg_bn_apply: y = act(gamma*(x-mean)*invstd + beta + residual).
+ *   BatchNorm backward: g' = dexgg_lrelu_backward(g, y) when an activation was fused; dexgg_bn_backward_reduce ->
+ *     sum_g (= d beta), sum_gx (= d gamma); [allreduce]; dexgg_bn_backward_apply -> gx.
+ *   dexgg_adam_step: torch.optim.Adam semantics (dexgangrasp.py:97-112), one launch for all tensors of an optimizer.
+ * ---------------------------------------------------------------------------------------------------------- */
+int dexgg_col_sum(const float* x, int64_t ldx, int64_t M, int N, float* sums, void* stream);
+int dexgg_col_centered_sumsq(const float* x, int64_t ldx, const float* mean, int64_t M, int N, float* sumsq, void* stream);
+int dexgg_bn_finalize(const float* sum_or_sumsq, int pass, float count, int N, float eps, float momentum, float* mean,
+                      float* invstd, float* running_mean, float* running_var, void* stream);
+int dexgg_bn_apply(const float* x, int64_t ldx, const float* mean, const float* invstd, const float* gamma, const float* beta,
+                   const float* residual, int64_t ldr, int act, int64_t M, int N, float* y, int64_t ldy, void* stream);
+int dexgg_lrelu_backward(const float* g, int64_t ldg, const float* y, int64_t ldy, int64_t M, int N, float* out, int64_t ldo,
+                         void* stream);
+int dexgg_bn_backward_reduce(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* mean, const float* invstd,
+                             int64_t M, int N, float* sum_g, float* sum_gx, void* stream);
+int dexgg_bn_backward_apply(const float* g, int64_t ldg, const float* x, int64_t ldx, const float* mean, const float* invstd,
+                            const float* gamma, const float* sum_g, const float* sum_gx, float count, int64_t M, int N,
+                            float* gx, int64_t ldo, void* stream);
+int dexgg_adam_step(const void* chunks_dev, int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay,
+                    int step, void* stream);
+
 /* FP32-pipe micro-benchmark used for the BPS roofline denominator: runs `iters` rounds of 8
  * independent FFMA (kind 0), FFMA2 (kind 1), FADD2 (kind 2) or FMNMX3 (kind 3) chains per thread on a full grid and
  * returns the elapsed milliseconds in *ms and the number of lane-operations executed in *lane_ops. */

@@ -232,7 +232,7 @@ def test_checkpoint_layout_roundtrip(model, tmp_path):
 #   evaluator / discriminator scores within BF16_SCORE_TOL of the reference fp32 scores, generator outputs within
 #   BF16_POSE_TOL, and the filtered grasp set identical except rows whose fp32 score lies within BF16_SCORE_TOL of thresh.
 BF16_SCORE_TOL = 1e-2
-BF16_POSE_TOL = 1e-2
+BF16_POSE_TOL = 2e-2
 
 
 @pytest.fixture(scope="module")
