@@ -103,8 +103,9 @@ class DexGanGrasp(object):
             self.conf_coef = 10.
             self.train_dexgenerator = cfg["train_ffhgenerator"]
             self.train_dexevaluator = cfg["train_ffhevaluator"]
-            adam = lambda params, lr: torch.optim.Adam(params, lr=lr, betas=(cfg["beta1"], 0.999),
-                                                       weight_decay=cfg["weight_decay"])
+            from .train_ops import DexggAdam  # torch.optim.Adam state / state_dict, one fused CUDA launch per step
+            adam = lambda params, lr: DexggAdam(params, lr=lr, betas=(cfg["beta1"], 0.999),
+                                                weight_decay=cfg["weight_decay"])
             self.optim_dexgenerator = adam(self.DexGANGrasp.parameters(), cfg["lr"])
             self.optim_dexgangrasp_generator = adam(self.DexGANGrasp.generator.parameters(), cfg["lr_gen"])
             self.optim_dexgangrasp_discriminator = adam(self.DexGANGrasp.discriminator.parameters(), cfg["lr_dis"])
@@ -359,7 +360,16 @@ class DexGanGrasp(object):
         if is_train_gen:
             fake_data = {"bps_object": real_data["bps_object"], "rot_matrix": y_fake["rot_matrix"], "rot_6D": fake_rot_6D,
                          "transl": fake_transl, "joint_conf": fake_joint_conf}
-            fake_score_gen = D(fake_data)
+            # The reference also back-propagates this pass into D's weights and throws the result away at the next
+            # zero_grad (dexgangrasp.py:808-816); freezing D here skips those wgrad GEMMs without changing any output.
+            d_params = [p for p in D.parameters() if p.requires_grad]
+            for p in d_params:
+                p.requires_grad_(False)
+            try:
+                fake_score_gen = D(fake_data)
+            finally:
+                for p in d_params:
+                    p.requires_grad_(True)
             real_data["rot_matrix"] = real_data["rot_matrix"].view(real_data["bps_object"].shape[0], -1)
             total_loss_gen, loss_dict_gen = self.compute_loss_dexgangrasp_generator(real_data, fake_data, fake_score_gen)
             self.optim_dexgangrasp_generator.zero_grad()

@@ -364,5 +364,5 @@ class DexEvaluator(nn.Module):
         self.set_input(data)
         if self.training:
             from . import train_ops as T
-            return T.evaluator_forward_train(self)
+            return T.evaluator_forward_train(self, getattr(self, "dropout_masks", None))
         return self.native_forward(self.bps_object, self.rot_matrix, self.transl)

@@ -1,0 +1,310 @@
+"""Train-mode forward / backward of the DexGenerator, Discriminator and DexEvaluator on the kernels of libdexgg.
+
+torch.autograd only records the graph: every Function below calls the C ABI (include/dexgg.h) for its arithmetic —
+dexgg_linear_f32 (forward, dgrad with trans_w, wgrad with trans_a), the train-mode BatchNorm kernels, LeakyReLU backward,
+column sums for the bias gradients, rot6d forward/backward (utils.py) and the multi-tensor Adam step.
+
+Reference: ResBlock.forward (DexGanGrasp/models/networks.py:43-56), Generator.forward (:88-103), Discriminator.forward
+(:148-159), DexEvaluator.forward (:315-337) in training mode, as driven by DexGanGrasp.update_dexgangrasp /
+update_dexevaluator (DexGanGrasp/models/dexgangrasp.py:739-823).
+
+Data parallelism: when torch.distributed is initialised with world_size > 1 the BatchNorm statistics
+(forward: sum, centred sum of squares; backward: sum g, sum g*xhat) are summed over ranks, so the n-rank step equals the
+1-rank step on the concatenated batch.
+"""
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from . import _native
+
+BN_EPS = 1e-5
+
+
+def _L():
+    return _native.lib()
+
+
+def _st(dev):
+    return _native.stream_ptr(dev)
+
+
+def _world():
+    return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+
+
+def _allreduce_sum(t):
+    if _world() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+
+
+def _check_cuda(x):
+    if not x.is_cuda:
+        raise RuntimeError("dexgg: training tensors must be on a CUDA (B200) device; there is no CPU path")
+
+
+def _rowmajor(x):
+    """A 2-D fp32 tensor whose rows are contiguous (any row pitch); copies only if needed."""
+    if x.dtype != torch.float32:
+        x = x.float()
+    if x.dim() != 2 or x.stride(1) != 1 or (x.shape[0] > 1 and x.stride(0) < x.shape[1]):
+        x = x.contiguous()
+    return x
+
+
+def _ld(x):
+    return x.stride(0) if x.shape[0] > 1 else x.shape[1]
+
+
+def raw_linear(A, trans_a, W, trans_w, M, N, K, bias=None, act=0, accumulate=0, out=None):
+    """C[M,N] = act(op(A) . op(W)^T + bias) through dexgg_linear_f32."""
+    dev = A.device
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _native.check(_L().dexgg_linear_f32(A.data_ptr(), _ld(A), int(trans_a), W.data_ptr(), _ld(W), int(trans_w), M, N, K,
+                                            _native.ptr(bias), None, None, None, 0, int(act), int(accumulate),
+                                            out.data_ptr(), _ld(out), _st(dev)))
+    return out
+
+
+def col_sum(x):
+    M, N = x.shape
+    s = torch.zeros((N,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _native.check(_L().dexgg_col_sum(x.data_ptr(), _ld(x), M, N, s.data_ptr(), _st(x.device)))
+    return s
+
+
+def lrelu_backward(g, y):
+    M, N = g.shape
+    out = torch.empty((M, N), dtype=torch.float32, device=g.device)
+    with torch.cuda.device(g.device):
+        _native.check(_L().dexgg_lrelu_backward(g.data_ptr(), _ld(g), y.data_ptr(), _ld(y), M, N, out.data_ptr(), N, _st(g.device)))
+    return out
+
+
+class _LinearFn(torch.autograd.Function):
+    """y = act(x W^T + b)   (nn.Linear [+ LeakyReLU(0.2)], networks.py:31-41)"""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, act):
+        _check_cuda(x)
+        x = _rowmajor(x)
+        M, K = x.shape
+        N = weight.shape[0]
+        y = raw_linear(x, 0, weight, 0, M, N, K, bias=bias, act=1 if act else 0)
+        ctx.act = bool(act)
+        ctx.save_for_backward(x, weight, y if act else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, weight, y = ctx.saved_tensors
+        g = _rowmajor(g)
+        if ctx.act:
+            g = lrelu_backward(g, y)
+        M, K = x.shape
+        N = weight.shape[0]
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:  # dgrad: gx[m,k] = sum_n g[m,n] W[n,k]
+            gx = raw_linear(g, 0, weight, 1, M, K, N)
+        if ctx.needs_input_grad[1]:  # wgrad: gw[n,k] = sum_m g[m,n] x[m,k]
+            gw = raw_linear(g, 1, x, 1, N, K, M)
+        if ctx.needs_input_grad[2]:
+            gb = col_sum(g)
+        return gx, gw, gb, None
+
+
+def linear(x, weight, bias, act=False):
+    return _LinearFn.apply(x, weight, bias, act)
+
+
+class _BatchNormFn(torch.autograd.Function):
+    """y = act(gamma * (x - mean_batch) / sqrt(var_batch + eps) + beta [+ residual]); running stats updated in place
+    (momentum 0.1, unbiased variance) like nn.BatchNorm1d in training mode."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, momentum, act):
+        _check_cuda(x)
+        x = _rowmajor(x)
+        M, N = x.shape
+        dev = x.device
+        L = _L()
+        count = float(M * _world())
+        mean = torch.empty((N,), dtype=torch.float32, device=dev)
+        invstd = torch.empty((N,), dtype=torch.float32, device=dev)
+        s = col_sum(x)
+        _allreduce_sum(s)
+        with torch.cuda.device(dev):
+            st = _st(dev)
+            _native.check(L.dexgg_bn_finalize(s.data_ptr(), 0, count, N, BN_EPS, momentum, mean.data_ptr(), None, None, None, st))
+            ss = torch.zeros((N,), dtype=torch.float32, device=dev)
+            _native.check(L.dexgg_col_centered_sumsq(x.data_ptr(), _ld(x), mean.data_ptr(), M, N, ss.data_ptr(), st))
+            _allreduce_sum(ss)
+            _native.check(L.dexgg_bn_finalize(ss.data_ptr(), 1, count, N, BN_EPS, momentum, mean.data_ptr(), invstd.data_ptr(),
+                                              _native.ptr(running_mean), _native.ptr(running_var), st))
+            y = torch.empty((M, N), dtype=torch.float32, device=dev)
+            res = _rowmajor(residual) if residual is not None else None
+            _native.check(L.dexgg_bn_apply(x.data_ptr(), _ld(x), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                                           beta.data_ptr(), _native.ptr(res), _ld(res) if res is not None else 0,
+                                           1 if act else 0, M, N, y.data_ptr(), N, st))
+        ctx.act = bool(act)
+        ctx.count = count
+        ctx.has_res = residual is not None
+        ctx.save_for_backward(x, gamma, mean, invstd, y if act else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, gamma, mean, invstd, y = ctx.saved_tensors
+        g = _rowmajor(g)
+        if ctx.act:
+            g = lrelu_backward(g, y)
+        M, N = x.shape
+        dev = x.device
+        L = _L()
+        sum_g = torch.zeros((N,), dtype=torch.float32, device=dev)
+        sum_gx = torch.zeros((N,), dtype=torch.float32, device=dev)
+        gx = None
+        with torch.cuda.device(dev):
+            st = _st(dev)
+            _native.check(L.dexgg_bn_backward_reduce(g.data_ptr(), _ld(g), x.data_ptr(), _ld(x), mean.data_ptr(), invstd.data_ptr(),
+                                                     M, N, sum_g.data_ptr(), sum_gx.data_ptr(), st))
+            g_gamma, g_beta = sum_gx, sum_g  # local sums; the gradient allreduce averages them over ranks
+            if ctx.needs_input_grad[0]:
+                tot_g, tot_gx = sum_g, sum_gx
+                if _world() > 1:
+                    both = torch.stack([sum_g, sum_gx])
+                    _allreduce_sum(both)
+                    tot_g, tot_gx = both[0].contiguous(), both[1].contiguous()
+                gx = torch.empty((M, N), dtype=torch.float32, device=dev)
+                _native.check(L.dexgg_bn_backward_apply(g.data_ptr(), _ld(g), x.data_ptr(), _ld(x), mean.data_ptr(),
+                                                        invstd.data_ptr(), gamma.data_ptr(), tot_g.data_ptr(), tot_gx.data_ptr(),
+                                                        ctx.count, M, N, gx.data_ptr(), N, st))
+        g_res = g if (ctx.has_res and ctx.needs_input_grad[3]) else None
+        return gx, (g_gamma if ctx.needs_input_grad[1] else None), (g_beta if ctx.needs_input_grad[2] else None), g_res, None, None, None, None
+
+
+def batch_norm(x, bn, act=False, residual=None, final_act=True):
+    """Train-mode nn.BatchNorm1d `bn` applied to x, optionally followed by `+ residual` and LeakyReLU(0.2).
+    act: LeakyReLU directly after the normalisation (ResBlock bn1); residual/final_act: ResBlock tail (networks.py:53-56)."""
+    do_act = bool(act) or (residual is not None and bool(final_act))
+    if bn.training:
+        y = _BatchNormFn.apply(x, bn.weight, bn.bias, residual, bn.running_mean if bn.track_running_stats else None,
+                               bn.running_var if bn.track_running_stats else None,
+                               0.1 if bn.momentum is None else float(bn.momentum), do_act)
+        if bn.track_running_stats and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked += 1
+        return y
+    raise RuntimeError("dexgg: eval-mode BatchNorm goes through the packed forward (dexgg_*_forward), not train_ops")
+
+
+# ---------------------------------------------------------------------------------------------------- module forwards
+def resblock(rb, x, final_nl=True):
+    """ResBlock.forward (networks.py:43-56)"""
+    Xin = x if rb.Fin == rb.Fout else linear(x, rb.fc3.weight, rb.fc3.bias, act=True)
+    h = linear(x, rb.fc1.weight, rb.fc1.bias)
+    h = batch_norm(h, rb.bn1, act=True)
+    h = linear(h, rb.fc2.weight, rb.fc2.bias)
+    return batch_norm(h, rb.bn2, act=False, residual=Xin, final_act=final_nl)
+
+
+def generator_forward_train(gen, Zin, bps_object):
+    """Generator.forward (networks.py:88-103), training mode: z FIRST in X0, X0 FIRST in the rb2 input."""
+    dev = gen.gen_bn1.weight.device
+    bps = bps_object.to(device=dev, dtype=torch.float32)
+    z = Zin.to(device=dev, dtype=torch.float32)
+    o_bps = batch_norm(bps, gen.gen_bn1)
+    X0 = torch.cat([z, o_bps], dim=1)
+    X = gen.gen_rb1(X0, True)
+    X = gen.gen_rb2(torch.cat([X0, X], dim=1), True)
+    return {
+        "rot_6D": linear(X, gen.gen_rot.weight, gen.gen_rot.bias),
+        "transl": linear(X, gen.gen_transl.weight, gen.gen_transl.bias),
+        "joint_conf": linear(X, gen.gen_joint_conf.weight, gen.gen_joint_conf.bias),
+        "z": Zin,
+    }
+
+
+def discriminator_forward_train(disc):
+    """Discriminator.forward (networks.py:148-159) on the tensors set_input stored; X0 FIRST in the rb2 input."""
+    X = torch.cat([disc.bps_object, disc.rot_matrix, disc.transl, disc.joint_conf], dim=1)
+    X0 = batch_norm(X, disc.disc_bn1)
+    X = disc.disc_rb1(X0)
+    X = disc.disc_rb2(torch.cat([X0, X], dim=1))
+    return torch.sigmoid(linear(X, disc.out_success.weight, disc.out_success.bias))
+
+
+def evaluator_forward_train(eva, dropout_masks=None):
+    """DexEvaluator.forward (networks.py:315-337), training mode: X FIRST in the rb2/rb3 inputs, Dropout(0.3) after every
+    block.  dropout_masks (optional, three pre-scaled keep masks) replaces torch's Philox stream in parity tests."""
+    def dout(x, i):
+        if dropout_masks is not None:
+            return x * dropout_masks[i]
+        return eva.dout(x)
+    X = torch.cat([eva.bps_object, eva.rot_matrix, eva.transl], dim=1)
+    X0 = batch_norm(X, eva.bn1)
+    X = dout(eva.rb1(X0), 0)
+    X = dout(eva.rb2(torch.cat([X, X0], dim=1)), 1)
+    X = dout(eva.rb3(torch.cat([X, X0], dim=1)), 2)
+    return torch.sigmoid(linear(X, eva.out_success.weight, eva.out_success.bias))
+
+
+# ---------------------------------------------------------------------------------------------------- optimizer
+class _AdamChunk(ctypes.Structure):
+    _fields_ = [("w", ctypes.c_void_p), ("g", ctypes.c_void_p), ("m", ctypes.c_void_p), ("v", ctypes.c_void_p), ("n", ctypes.c_int)]
+
+
+class DexggAdam(torch.optim.Adam):
+    """torch.optim.Adam (dexgangrasp.py:97-112: betas (beta1, 0.999), coupled weight decay) whose step() is ONE
+    dexgg_adam_step launch over all parameters of a group.  State layout ('step', 'exp_avg', 'exp_avg_sq') and state_dict
+    are torch's, so optimizer checkpoints written by the reference load unchanged."""
+
+    CHUNK = 1 << 16
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        for group in self.param_groups:
+            if group.get("amsgrad") or group.get("maximize"):
+                raise NotImplementedError("DexggAdam: amsgrad / maximize are not used by the reference")
+            params = [p for p in group["params"] if p.grad is not None]
+            if not params:
+                continue
+            dev = params[0].device
+            _check_cuda(params[0])
+            steps = set()
+            chunks = []
+            for p in params:
+                st = self.state[p]
+                if len(st) == 0:
+                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                    st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                    st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                st["step"] += 1
+                steps.add(int(st["step"].item()) if torch.is_tensor(st["step"]) else int(st["step"]))
+                g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+                if g is not p.grad:
+                    p.grad = g
+                n = p.numel()
+                for o in range(0, n, self.CHUNK):
+                    c = min(self.CHUNK, n - o)
+                    chunks.append((p.data_ptr() + 4 * o, g.data_ptr() + 4 * o, st["exp_avg"].data_ptr() + 4 * o,
+                                   st["exp_avg_sq"].data_ptr() + 4 * o, c))
+            if len(steps) != 1:
+                raise RuntimeError("DexggAdam: parameters of one group must share the step count")
+            key = tuple(chunks)
+            if getattr(self, "_table_key", None) != key:  # chunk table lives on the device; rebuilt only when pointers move
+                arr = (_AdamChunk * len(chunks))(*[_AdamChunk(*c) for c in chunks])
+                self._table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(dev)
+                self._table_key = key
+            b1, b2 = group["betas"]
+            lr = group["lr"]
+            with torch.cuda.device(dev):
+                _native.check(_L().dexgg_adam_step(self._table.data_ptr(), len(chunks), float(lr), float(b1), float(b2),
+                                                   float(group["eps"]), float(group["weight_decay"]), steps.pop(), _st(dev)))
+            # parameters changed behind torch's back: bump versions so packed inference weights refresh
+            torch.autograd.graph.increment_version(params)
+        return loss

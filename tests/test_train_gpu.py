@@ -1,0 +1,168 @@
+"""GPU parity of the training step (DexGanGrasp.update_dexgangrasp / update_dexevaluator, reference
+DexGanGrasp/models/dexgangrasp.py:739-823) run on the train-mode kernels of libdexgg, against the CPU oracle
+(oracle/nets_oracle.py: torch-CPU autograd on the functional restatement + restated Adam) from identical state.
+
+Tolerances: losses 1e-4 absolute, BatchNorm running statistics 1e-5, weights after one Adam step 1e-5
+(Adam's first step moves every weight by ~lr = 1e-4 whatever the gradient scale, so the gradients themselves are also
+compared, in the relative L2 norm — see grad_close)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from dex_gan_grasp_b200 import synth
+from oracle import nets_oracle as no
+
+pytestmark = pytest.mark.gpu
+SEED = 7
+CFG = dict(latentD=5, n_hand_joints=12, is_train=True, gpu_ids=[0], model="dexgangrasp", is_wgan=False, bce_weight=1.0,
+           train_ffhgenerator=True, train_ffhevaluator=True, beta1=0.9, weight_decay=5e-4, lr=1e-4, lr_gen=1e-4, lr_dis=1e-4,
+           lr_policy="plateau", threshold_lr_policy_plateau=0.01, patience_lr_policy_plateau=5, weight_init_type="xavier",
+           init_gain=0.02)
+B = 192
+
+
+def md(a, b):
+    a = a.detach().cpu().double().reshape(-1)
+    b = b.detach().cpu().double().reshape(-1)
+    return float((a - b).abs().max())
+
+
+@pytest.fixture()
+def model():
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    m = DexGanGrasp(dict(CFG))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    return m
+
+
+def _batch():
+    return synth.synth_train_batch(B, seed=11)
+
+
+def grad_close(got, ref, what):
+    """Gradients are compared in the relative L2 norm, 5e-3.  Agreement is ~1e-6 when no LeakyReLU pre-activation of the
+    batch lies within fp32 rounding of zero; when one does, its sign (slope 1 vs 0.2) legitimately differs between two
+    correct fp32 implementations and moves a few gradient entries by percents of the max (seen torch-CUDA vs torch-CPU
+    too), so a max-norm test is flaky by construction.  Any real defect (missing term, wrong scale) is O(0.1-1) here."""
+    assert got is not None, what
+    ref = ref.double()
+    den = float(ref.norm())
+    if what[1].endswith(("fc1.bias", "fc2.bias")):  # a bias in front of a train-mode BatchNorm: the true gradient is
+        assert den < 1e-5 and float(got.detach().cpu().double().norm()) < 1e-5, what  # zero, both sides hold rounding noise
+        return
+    err = float((got.detach().cpu().double() - ref).norm()) / den
+    assert err < 5e-3, (what, err)
+
+
+def _check_state(module, sd_ref, grads=None, w0=None, lr=1e-4, steps=1, wd=5e-4):
+    """Buffers (BatchNorm running statistics) at 1e-5.  Weights after Adam: an element whose gradient is far from zero
+    must agree at 1e-5; where g + wd*w is within rounding noise of zero, Adam's g/(|g|+eps) amplifies that noise up to the
+    full step lr (in a 1M-element tensor a few hundred elements always are), so those elements are only bounded by 2*lr
+    per step.  This is a property of Adam, equally true torch-vs-torch."""
+    sd = module.state_dict()
+    params = {k for k, _ in module.named_parameters()}
+    for k, v in sd_ref.items():
+        if not v.is_floating_point():
+            assert int(sd[k]) == int(v), k
+            continue
+        err = (sd[k].detach().cpu().double() - v.double()).abs()
+        if k not in params:
+            assert float(err.max()) < (1e-5 if steps == 1 else 2e-4) * max(1.0, float(v.abs().max())), (k, float(err.max()))
+            continue
+        assert float(err.max()) <= 2.1 * lr * steps, (k, float(err.max()))
+        if grads is not None and k in grads:
+            g = (grads[k] + wd * w0[k]).abs()  # torch.optim.Adam couples the weight decay into the gradient
+            solid = g > 1e-3 * float(g.max())
+            if solid.any():  # (a LeakyReLU sign flip, see grad_close, can still turn the sign of a few of them)
+                frac = float((err[solid] < 1e-5).double().mean())
+                assert frac > 0.995, (k, frac, float(err[solid].max()))
+        else:
+            assert float((err < 1e-5).double().mean()) > 0.98, (k, float((err < 1e-5).double().mean()))
+
+
+def test_gan_step_matches_oracle(model):
+    batch = _batch()
+    z = synth.synth_latents(B, 5, seed=3)
+    sd = {k: v.clone() for k, v in synth.synth_gan_state_dict(SEED).items()}
+    opt_d, opt_g = {}, {}
+    ref_losses, ref_grads = no.gan_step(sd, opt_d, opt_g, copy.deepcopy(batch), z.clone(), is_train_gen=True)
+
+    # capture gradients of our step
+    ours = model.update_dexgangrasp(copy.deepcopy(batch), is_train_gen=True, Zgen=z.cuda())
+    torch.cuda.synchronize()
+    for k, v in ref_losses.items():
+        assert abs(float(ours[k]) - v) < 1e-4 * max(1.0, abs(v)), (k, float(ours[k]), v)
+    named = dict(model.DexGANGrasp.named_parameters())
+    for k, g in ref_grads["g"].items():
+        grad_close(named[k].grad, g, ("G grad", k))
+    _check_state(model.DexGANGrasp, sd, {**ref_grads["d"], **ref_grads["g"]}, synth.synth_gan_state_dict(SEED))
+
+
+def test_gan_step_without_generator_update(model):
+    batch = _batch()
+    z = synth.synth_latents(B, 5, seed=4)
+    sd = {k: v.clone() for k, v in synth.synth_gan_state_dict(SEED).items()}
+    ref_losses, ref_grads = no.gan_step(sd, {}, {}, copy.deepcopy(batch), z.clone(), is_train_gen=False)
+    ours = model.update_dexgangrasp(copy.deepcopy(batch), is_train_gen=False, Zgen=z.cuda())
+    for k, v in ref_losses.items():
+        assert abs(float(ours[k]) - v) < 1e-4 * max(1.0, abs(v)), k
+    named = dict(model.DexGANGrasp.named_parameters())
+    for k, g in ref_grads["d"].items():
+        grad_close(named[k].grad, g, ("D grad", k))
+    _check_state(model.DexGANGrasp, sd, ref_grads["d"], synth.synth_gan_state_dict(SEED))
+
+
+def test_two_gan_steps_adam_state(model):
+    """Second step exercises the Adam moments and the re-packed weights."""
+    sd = {k: v.clone() for k, v in synth.synth_gan_state_dict(SEED).items()}
+    opt_d, opt_g = {}, {}
+    for it in range(2):
+        batch = synth.synth_train_batch(B, seed=20 + it)
+        z = synth.synth_latents(B, 5, seed=30 + it)
+        ref_losses, _ = no.gan_step(sd, opt_d, opt_g, copy.deepcopy(batch), z.clone())
+        ours = model.update_dexgangrasp(copy.deepcopy(batch), Zgen=z.cuda())
+        for k, v in ref_losses.items():
+            assert abs(float(ours[k]) - v) < 2e-4 * max(1.0, abs(v)), (it, k, float(ours[k]), v)
+    _check_state(model.DexGANGrasp, sd, steps=2)
+    st = model.optim_dexgangrasp_generator.state_dict()["state"]
+    assert all(set(s.keys()) == {"step", "exp_avg", "exp_avg_sq"} for s in st.values())  # torch.optim.Adam checkpoint layout
+
+
+def test_evaluator_step_matches_oracle(model):
+    batch = _batch()
+    g = torch.Generator().manual_seed(5)
+    masks = [(torch.rand(B, 512, generator=g) >= 0.3).float() / 0.7 for _ in range(3)]  # Dropout(0.3) keep masks, pre-scaled
+    sd = {k: v.clone() for k, v in synth.synth_eva_state_dict(SEED).items()}
+    ref_losses, ref_grads = no.evaluator_step(sd, {}, copy.deepcopy(batch), dropout_masks=masks)
+    model.DexEvaluator.dropout_masks = [m.cuda() for m in masks]
+    ours = model.update_dexevaluator(copy.deepcopy(batch))
+    model.DexEvaluator.dropout_masks = None
+    for k, v in ref_losses.items():
+        assert abs(float(ours[k]) - v) < 1e-4 * max(1.0, abs(v)), k
+    named = dict(model.DexEvaluator.named_parameters())
+    for k, gr in ref_grads.items():
+        grad_close(named[k].grad, gr, ("E grad", k))
+    _check_state(model.DexEvaluator, sd, ref_grads, synth.synth_eva_state_dict(SEED))
+
+
+def test_evaluator_step_with_torch_dropout_runs(model):
+    """Fast mode: torch's own Philox dropout stream; the loss must be finite and the weights must move."""
+    before = model.DexEvaluator.out_success.weight.detach().clone()
+    out = model.update_dexevaluator(_batch())
+    assert np.isfinite(float(out["total_loss_eva"]))
+    assert md(before, model.DexEvaluator.out_success.weight) > 0
+
+
+def test_eval_losses_after_training(model):
+    """eval_* helpers (dexgangrasp.py:309-365) run the packed eval-mode forward on the just-updated weights."""
+    batch = _batch()
+    model.update_dexgangrasp(copy.deepcopy(batch))
+    d = model.eval_dexgangrasp_generator_loss(copy.deepcopy(batch))
+    assert all(np.isfinite(float(v)) for v in d.values())
+    e = model.eval_dexevaluator_loss(copy.deepcopy(batch))
+    assert np.isfinite(float(e["total_loss_eva"]))
+    pos, neg, pred, gt = model.eval_dexevaluator_accuracy(copy.deepcopy(batch))
+    assert pred.shape == gt.shape
