@@ -43,3 +43,35 @@ def shard(batch, rank=None, world=None):
         else:
             out[k] = v
     return out
+
+
+def shard_objects(n_objects, rank=None, world=None):
+    """Inference sharding: rank r owns objects [lo, hi) with ALL their latent samples, so the per-object
+    BPS projection stays rank-local and no collective is needed.  Remainders go to the first ranks."""
+    if rank is None:
+        rank, world = (dist.get_rank(), dist.get_world_size()) if is_parallel() else (0, 1)
+    base, rem = divmod(int(n_objects), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def object_seed(seed, object_id):
+    """Seed of object `object_id`'s latent stream: results do not depend on how objects are spread over GPUs."""
+    return (int(seed) * 1000003 + int(object_id)) & 0x7FFFFFFF
+
+
+def batchnorm_statistics(x, eps=1e-5):
+    """The two-pass cross-rank statistics protocol of train_ops._BatchNormFn, on plain tensors (any device): allreduce
+    the column sums -> global mean, allreduce the centred sums of squares -> biased variance.  Returns (mean, invstd,
+    unbiased variance, global row count).  train_ops runs the same sequence with the CUDA reduction kernels."""
+    world = dist.get_world_size() if is_parallel() else 1
+    count = float(x.shape[0] * world)
+    s = x.sum(0)
+    if world > 1:
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+    mean = s / count
+    ss = ((x - mean) ** 2).sum(0)
+    if world > 1:
+        dist.all_reduce(ss, op=dist.ReduceOp.SUM)
+    var = ss / count
+    return mean, 1.0 / torch.sqrt(var + eps), var * (count / max(count - 1.0, 1.0)), count
