@@ -1,0 +1,56 @@
+// Fused whole-network tensor-core kernel (chain_umma.cu): interface used by nets.cu.
+//
+// One CTA takes a tile of 128 grasps through EVERY layer of the DexGenerator or the DexEvaluator (eval-mode BatchNorm,
+// per-object hoisted BPS projection): activations never leave the SM (shared memory as the tcgen05 A operand, TMEM for the
+// accumulators and the packed residual), the weights are streamed from L2 as a pre-swizzled tile stream by bulk TMA
+// copies, and the heads (rot6d -> SO(3) + palm offset + joints, or sigmoid score) are applied from TMEM in the last
+// epilogue.  Reference: ResBlock.forward / Generator.forward / DexEvaluator.forward, DexGanGrasp/models/networks.py:43-56,
+// 88-103, 315-337; utils.rot_matrix_from_ortho6d (utils/utils.py:380-394); utils.translate_along_axis (utils/utils.py:19-48).
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace dexgg {
+
+constexpr int CH_MAX_BLOCKS = 3;
+
+struct ChainPackSrc {          // fp32 packed weights of nets.cu (device pointers)
+    int kind;                  // DEXGG_NET_GENERATOR or DEXGG_NET_EVALUATOR
+    int n_blocks;
+    int tailw;                 // must be 16
+    int nh;                    // head rows: nJ + 9 (generator) or 1 (evaluator)
+    const float* Wt[CH_MAX_BLOCKS];  // [768, KT]: cols [X 512 (if has_x) | tail (tailw)]
+    int KT[CH_MAX_BLOCKS];
+    int has_x[CH_MAX_BLOCKS];
+    const float* W2[CH_MAX_BLOCKS];  // [512, 256]
+    const float* Wh;                 // [nh, 512]
+};
+
+struct ChainArgs {
+    int kind, n_blocks, nJ, nh;
+    const __nv_bfloat16* stream;     // weight tile stream built by chain_pack
+    int has_x[CH_MAX_BLOCKS];
+    const float* sc[CH_MAX_BLOCKS];  // [768] affine of the first layer (bn1 on the fc1 rows, identity on the fc3 rows)
+    const float* sh[CH_MAX_BLOCKS];
+    const float* sc2[CH_MAX_BLOCKS];  // [512] bn2 affine (fc2 bias folded)
+    const float* sh2[CH_MAX_BLOCKS];
+    const float* base;               // [n_obj, 768 * n_blocks] per-object hoisted projection
+    int64_t n_obj, rows_per_obj, M;
+    const float* bh;                 // head bias
+    // generator
+    const float* z;                  // [M, zD]
+    int zD;
+    float z_offset;
+    float *rot, *transl, *joint, *rot6d;
+    // evaluator
+    const float *in_rot, *in_transl; // [M,9], [M,3]
+    const float *tail_a, *tail_c;    // input BatchNorm affine of the 12 pose columns
+    float* p;                        // [M]
+};
+
+size_t chain_stream_bytes(int kind, int n_blocks, const int* has_x);
+int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st);
+int chain_forward(const ChainArgs& a, cudaStream_t st);
+
+}  // namespace dexgg

@@ -1,0 +1,483 @@
+// Fused whole-network tcgen05 kernel for the DexGenerator / DexEvaluator forwards (eval-mode BatchNorm, hoisted BPS
+// projection).  See chain.cuh for the interface and DESIGN.md §4 for the roofline.
+//
+// One persistent CTA per SM, 320 threads, one 128-grasp tile at a time:
+//   warp 0      weight producer: walks the pre-swizzled weight tile stream (built once by chain_pack) with 1-D bulk TMA
+//               copies into a 5-stage x 16 KB shared-memory ring (mbarrier expect_tx / complete_tx)
+//   warp 1      MMA issuer: one thread issues tcgen05.mma.kind::f16 (M=128, N=128, K=16); A = activation k-blocks resident
+//               in shared memory (9 slots x [128 rows x 64 bf16], 128B swizzle), B = ring stage, D = TMEM
+//   warps 2..9  epilogue: tcgen05.ld -> per-object base + BatchNorm affine + LeakyReLU -> bf16 -> next layer's A operand in
+//               shared memory (or packed back into TMEM with tcgen05.st for the residual branch)
+// Per ResBlock (ResBlock.forward, networks.py:43-56), with X the 512-wide input (slots 0..7) and t the tail k-block (slot 8):
+//   P1  D[0,512)   = [X|t] . W3^T                         fc3 (skip branch), 4 x N=128
+//   E1  R = bf16(lrelu(D + base3)) packed two per column into TMEM [0,128) and [256,384)
+//   P2  D[128,256) , D[384,512) = [X|t] . W1^T            fc1, 2 x N=128
+//   E2  H = bf16(lrelu(sc*(D + base1) + sh)) -> slots 0..3 (X is dead now)
+//   P3  D[128,256) , D[384,512) = H . W2[0:256]^T ;  E3  Xout[:, 0:256]  = bf16(lrelu(R + sc2*D + sh2)) -> slots 4..7
+//   P4  same for W2[256:512]                        ;  E4  Xout[:, 256:512] -> slots 0..3 (H is dead now)
+// so every block leaves X columns 0..255 in slots 4..7 and columns 256..511 in slots 0..3; the stream is packed in that
+// k-block order.  Heads: one N=32 (generator) / N=16 (evaluator, weight as hi+lo rows) MMA chain over the 8 X slots, then
+// rot6d -> SO(3) + palm offset (utils.py:380-394, 19-48) or the sigmoid, straight from TMEM.
+#include "chain.cuh"
+#include "umma.cuh"
+
+namespace dexgg {
+
+constexpr int CH_SLOT_BYTES = 16384, CH_NSLOT = 9, CH_STAGES = 5, CH_THREADS = 320, CH_HEAD_TILES = 8;
+constexpr int CH_A_BYTES = CH_NSLOT * CH_SLOT_BYTES;
+constexpr int CH_SMEM_BYTES = CH_A_BYTES + CH_STAGES * CH_SLOT_BYTES + 256 + 1024;
+constexpr int CH_TAIL_SLOT = 8;
+#define CH_LRELU(v) ((v) > 0.f ? (v) : 0.2f * (v))
+
+__host__ __device__ inline int ch_block_tiles(int has_x) { return has_x ? 70 : 22; }  // fc3 4/kb + fc1 2/kb + fc2 16
+__host__ __device__ inline int ch_head_rows(int kind) { return kind == DEXGG_NET_GENERATOR ? 32 : 16; }
+
+// ---------------------------------------------------------------- weight stream packing
+struct ChTile {
+    const float* src;   // source matrix (fp32, row-major)
+    int ld, row0, nrows;  // rows [row0, row0 + nrows) are real, the rest of the tile is zero
+    int col0;           // first source column
+    int mode;           // 0: 64 plain columns; 1: tail [hi16|hi16|lo16|0]; 2: evaluator head (row 0 = hi, row 8 = lo)
+    int tile_rows;      // 128, 32 or 16
+    uint32_t pad;
+    uint64_t dst_off;   // byte offset of the tile in the stream
+};
+
+__global__ void chain_pack_kernel(const ChTile* __restrict__ tiles, unsigned char* __restrict__ stream) {
+    const ChTile t = tiles[blockIdx.x];
+    for (int e = threadIdx.x; e < t.tile_rows * 64; e += blockDim.x) {
+        const int r = e >> 6, c = e & 63;
+        float v = 0.f;
+        bool lo = false;
+        if (t.mode == 0) {
+            if (r < t.nrows) v = t.src[(int64_t)(t.row0 + r) * t.ld + t.col0 + c];
+        } else if (t.mode == 1) {
+            if (r < t.nrows && c < 48) {
+                v = t.src[(int64_t)(t.row0 + r) * t.ld + t.col0 + (c & 15)];
+                lo = c >= 32;
+            }
+        } else {
+            if (r == 0 || r == 8) {
+                v = t.src[t.col0 + c];
+                lo = r == 8;
+            }
+        }
+        __nv_bfloat16 hi = __float2bfloat16_rn(v);
+        if (lo) hi = __float2bfloat16_rn(v - __bfloat162float(hi));
+        const uint64_t off = t.dst_off + (uint64_t)r * 128 + (uint64_t)((((c >> 3) ^ (r & 7)) << 4) + ((c & 7) << 1));
+        *reinterpret_cast<__nv_bfloat16*>(stream + off) = hi;
+    }
+}
+
+// ---------------------------------------------------------------- TMEM helpers (16-column variants, store)
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]),
+        "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&h);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+// 32 consecutive bf16 columns (= 4 swizzle chunks starting at chunk `ci0`) of row `row` into an A-operand slot
+__device__ __forceinline__ void store_row32(unsigned char* slot, int row, int ci0, const float (&v)[32]) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint4 u = make_uint4(pack_bf16x2(v[8 * q], v[8 * q + 1]), pack_bf16x2(v[8 * q + 2], v[8 * q + 3]),
+                                   pack_bf16x2(v[8 * q + 4], v[8 * q + 5]), pack_bf16x2(v[8 * q + 6], v[8 * q + 7]));
+        *reinterpret_cast<uint4*>(slot + row * 128 + (((ci0 + q) ^ (row & 7)) << 4)) = u;
+    }
+}
+
+}  // namespace dexgg
+
+namespace dexgg {
+
+// ---------------------------------------------------------------- the kernel
+template <int KIND>
+__global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainArgs a) {
+    extern __shared__ unsigned char ch_smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ch_smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* sA = smem;                 // 9 activation k-block slots
+    unsigned char* sR = smem + CH_A_BYTES;    // weight ring
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sR + CH_STAGES * CH_SLOT_BYTES);
+    uint64_t* full = bars;                    // [STAGES]
+    uint64_t* empty = bars + CH_STAGES;       // [STAGES]
+    uint64_t* mma_bar = bars + 2 * CH_STAGES; // MMA phase complete -> epilogue
+    uint64_t* epi_bar = mma_bar + 1;          // epilogue phase complete (8 warps) -> MMA issuer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(epi_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ntiles = (int)((a.M + 127) / 128);
+    constexpr int HEAD_ROWS = KIND == DEXGG_NET_GENERATOR ? 32 : 16;
+    constexpr uint32_t HEAD_BYTES = HEAD_ROWS * 128;
+    int n_main = 0;
+    for (int b = 0; b < a.n_blocks; ++b) n_main += ch_block_tiles(a.has_x[b]);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < CH_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], 1);
+        }
+        mbar_init(mma_bar, 1);
+        mbar_init(epi_bar, 8);
+        mbar_fence_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== weight producer =====================
+        if (lane == 0) {
+            int stage = 0, phase = 0;
+            const unsigned char* src = reinterpret_cast<const unsigned char*>(a.stream);
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                size_t off = 0;
+                for (int i = 0; i < n_main + CH_HEAD_TILES; ++i) {
+                    const uint32_t bytes = i < n_main ? (uint32_t)CH_SLOT_BYTES : HEAD_BYTES;
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_expect_tx(&full[stage], bytes);
+                    bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, bytes, &full[stage]);
+                    off += bytes;
+                    if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_bf16(128, 128), idesc_h = umma_idesc_bf16(128, HEAD_ROWS);
+            const uint32_t sA_u = smem_u32(sA), sR_u = smem_u32(sR);
+            int stage = 0, phase = 0, ephase = 0;
+            auto wait_epi = [&]() {
+                mbar_wait(epi_bar, ephase);
+                ephase ^= 1;
+                tc_fence_after();
+            };
+            auto mma_tile = [&](uint32_t d_col, int slot, uint32_t id, bool first) {
+                mbar_wait(&full[stage], phase);
+                tc_fence_after();
+                const uint64_t ad = umma_desc_sw128_kmajor(sA_u + slot * CH_SLOT_BYTES);
+                const uint64_t bd = umma_desc_sw128_kmajor(sR_u + stage * CH_SLOT_BYTES);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + d_col, ad + 2 * k, bd + 2 * k, id, !(first && k == 0));
+                umma_commit(&empty[stage]);
+                if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
+            };
+            for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                for (int b = 0; b < a.n_blocks; ++b) {
+                    const int nkb = a.has_x[b] ? 9 : 1, s0 = a.has_x[b] ? 0 : CH_TAIL_SLOT;
+                    wait_epi();  // P1: fc3
+                    for (int i = 0; i < nkb; ++i)
+                        for (int q = 0; q < 4; ++q) mma_tile(q * 128, s0 + i, idesc, i == 0);
+                    umma_commit(mma_bar);
+                    wait_epi();  // P2: fc1
+                    for (int i = 0; i < nkb; ++i)
+                        for (int q = 0; q < 2; ++q) mma_tile(q ? 384 : 128, s0 + i, idesc, i == 0);
+                    umma_commit(mma_bar);
+                    for (int h = 0; h < 2; ++h) {  // P3 / P4: fc2 halves, A = H in slots 0..3
+                        wait_epi();
+                        for (int kb = 0; kb < 4; ++kb)
+                            for (int q = 0; q < 2; ++q) mma_tile(q ? 384 : 128, kb, idesc, kb == 0);
+                        umma_commit(mma_bar);
+                    }
+                }
+                wait_epi();  // heads over the 8 X slots
+                for (int s = 0; s < CH_HEAD_TILES; ++s) mma_tile(128, s, idesc_h, s == 0);
+                umma_commit(mma_bar);
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        const int row = quarter * 32 + lane;
+        const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        const int64_t ldbase = 768 * (int64_t)a.n_blocks;
+        int mphase = 0;
+        auto wait_mma = [&]() {
+            mbar_wait(mma_bar, mphase);
+            mphase ^= 1;
+            tc_fence_after();
+        };
+        auto arrive_epi = [&]() {
+            tc_fence_before();
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(epi_bar);
+        };
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            const int64_t m = (int64_t)t * 128 + row;
+            const int64_t mm = m < a.M ? m : a.M - 1;
+            const float* base_obj = a.base + (mm / a.rows_per_obj) * ldbase;
+            // ---- tail k-block (slot 8): per-row inputs as [hi16 | lo16 | hi16 | 0] ----
+            if (half == 0) {
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = 0.f;
+                if (KIND == DEXGG_NET_GENERATOR) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (j < a.zD) v[j] = a.z[mm * a.zD + j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 9; ++j) v[j] = fmaf(__ldg(a.tail_a + j), a.in_rot[mm * 9 + j], __ldg(a.tail_c + j));
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) v[9 + j] = fmaf(__ldg(a.tail_a + 9 + j), a.in_transl[mm * 3 + j], __ldg(a.tail_c + 9 + j));
+                }
+                float w[32];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    const float hi = __bfloat162float(__float2bfloat16_rn(v[j]));
+                    w[j] = hi;
+                    w[16 + j] = v[j] - hi;
+                }
+                unsigned char* slot = sA + CH_TAIL_SLOT * CH_SLOT_BYTES;
+                store_row32(slot, row, 0, w);  // chunks 0..3: hi | lo
+#pragma unroll
+                for (int j = 0; j < 16; ++j) { w[16 + j] = 0.f; }
+                store_row32(slot, row, 4, w);  // chunks 4..7: hi | 0
+            }
+            arrive_epi();
+            for (int b = 0; b < a.n_blocks; ++b) {
+                const float* base_b = base_obj + b * 768;
+                // ---- E1: skip branch R = bf16(lrelu(fc3 + base)), packed in place into TMEM ----
+                wait_mma();
+#pragma unroll 1
+                for (int c = 0; c < 8; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tlane + half * 256 + c * 32, r);
+                    tmem_ld_wait();
+                    const float* bp = base_b + 256 + half * 256 + c * 32;
+                    uint32_t o[16];
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 bv = *reinterpret_cast<const float4*>(bp + j);
+                        float x0 = __uint_as_float(r[j]) + bv.x, x1 = __uint_as_float(r[j + 1]) + bv.y;
+                        float x2 = __uint_as_float(r[j + 2]) + bv.z, x3 = __uint_as_float(r[j + 3]) + bv.w;
+                        o[j / 2] = pack_bf16x2(CH_LRELU(x0), CH_LRELU(x1));
+                        o[j / 2 + 1] = pack_bf16x2(CH_LRELU(x2), CH_LRELU(x3));
+                    }
+                    tmem_st_32x16(tlane + half * 256 + c * 16, o);
+                }
+                tmem_st_wait();
+                arrive_epi();
+                // ---- E2: H = bf16(lrelu(sc * (fc1 + base) + sh)) -> slots 0..3 ----
+                wait_mma();
+                {
+                    const float* sc = a.sc[b];
+                    const float* sh = a.sh[b];
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t r[32];
+                        tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
+                        tmem_ld_wait();
+                        const int n0 = half * 128 + c * 32;
+                        float v[32];
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            const float4 bv = *reinterpret_cast<const float4*>(base_b + n0 + j);
+                            const float4 s4 = __ldg(reinterpret_cast<const float4*>(sc + n0 + j));
+                            const float4 h4 = __ldg(reinterpret_cast<const float4*>(sh + n0 + j));
+                            float x0 = fmaf(__uint_as_float(r[j]) + bv.x, s4.x, h4.x), x1 = fmaf(__uint_as_float(r[j + 1]) + bv.y, s4.y, h4.y);
+                            float x2 = fmaf(__uint_as_float(r[j + 2]) + bv.z, s4.z, h4.z), x3 = fmaf(__uint_as_float(r[j + 3]) + bv.w, s4.w, h4.w);
+                            v[j] = CH_LRELU(x0); v[j + 1] = CH_LRELU(x1); v[j + 2] = CH_LRELU(x2); v[j + 3] = CH_LRELU(x3);
+                        }
+                        store_row32(sA + (half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
+                    }
+                }
+                arrive_epi();
+                // ---- E3 / E4: Xout = bf16(lrelu(R + sc2 * fc2 + sh2)) -> slots 4..7 (h = 0) / 0..3 (h = 1) ----
+                for (int h = 0; h < 2; ++h) {
+                    wait_mma();
+                    const float* sc2 = a.sc2[b];
+                    const float* sh2 = a.sh2[b];
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t r[32], rr[16];
+                        tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
+                        tmem_ld_32x16(tlane + h * 256 + half * 64 + c * 16, rr);
+                        tmem_ld_wait();
+                        const int n0 = h * 256 + half * 128 + c * 32;
+                        float v[32];
+#pragma unroll
+                        for (int j = 0; j < 32; j += 2) {
+                            const float2 s2 = __ldg(reinterpret_cast<const float2*>(sc2 + n0 + j));
+                            const float2 h2 = __ldg(reinterpret_cast<const float2*>(sh2 + n0 + j));
+                            float x0 = fmaf(__uint_as_float(r[j]), s2.x, h2.x) + bf16_lo(rr[j / 2]);
+                            float x1 = fmaf(__uint_as_float(r[j + 1]), s2.y, h2.y) + bf16_hi(rr[j / 2]);
+                            v[j] = CH_LRELU(x0); v[j + 1] = CH_LRELU(x1);
+                        }
+                        store_row32(sA + ((h ? 0 : 4) + half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
+                    }
+                    arrive_epi();
+                }
+            }
+            // ---- heads ----
+            wait_mma();
+            if (half == 0) {
+                if (KIND == DEXGG_NET_GENERATOR) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tlane + 128, r);
+                    tmem_ld_wait();
+                    if (m < a.M) {
+                        const int nJ = a.nJ;
+                        float hv[32];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) hv[j] = __uint_as_float(r[j]) + (j < a.nh ? __ldg(a.bh + j) : 0.f);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < nJ) a.joint[m * nJ + j] = hv[j];
+                        float g[9];
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)  // static indexing keeps hv in registers
+                            if (j >= nJ && j < nJ + 9) g[j - nJ] = hv[j];
+                        const float a0 = g[0], a1 = g[1], a2 = g[2], b0 = g[3], b1 = g[4], b2 = g[5];
+                        if (a.rot6d) {
+                            float* r6 = a.rot6d + m * 6;
+                            r6[0] = a0; r6[1] = a1; r6[2] = a2; r6[3] = b0; r6[4] = b1; r6[5] = b2;
+                        }
+                        const float na = fmaxf(sqrtf(a0 * a0 + a1 * a1 + a2 * a2), 1e-8f);
+                        const float x0 = a0 / na, x1 = a1 / na, x2 = a2 / na;
+                        float z0 = x1 * b2 - x2 * b1, z1 = x2 * b0 - x0 * b2, z2 = x0 * b1 - x1 * b0;
+                        const float nz = fmaxf(sqrtf(z0 * z0 + z1 * z1 + z2 * z2), 1e-8f);
+                        z0 /= nz; z1 /= nz; z2 /= nz;
+                        const float y0 = z1 * x2 - z2 * x1, y1 = z2 * x0 - z0 * x2, y2 = z0 * x1 - z1 * x0;
+                        float* ro = a.rot + m * 9;
+                        ro[0] = x0; ro[1] = y0; ro[2] = z0;
+                        ro[3] = x1; ro[4] = y1; ro[5] = z1;
+                        ro[6] = x2; ro[7] = y2; ro[8] = z2;
+                        const double off = (double)a.z_offset;
+                        a.transl[m * 3 + 0] = (float)((double)g[6] - (double)x0 * off);
+                        a.transl[m * 3 + 1] = (float)((double)g[7] - (double)x1 * off);
+                        a.transl[m * 3 + 2] = (float)((double)g[8] - (double)x2 * off);
+                    }
+                } else {
+                    uint32_t r[16];
+                    tmem_ld_32x16(tlane + 128, r);
+                    tmem_ld_wait();
+                    if (m < a.M) {
+                        const float s = __uint_as_float(r[0]) + __uint_as_float(r[8]) + __ldg(a.bh);
+                        a.p[m] = 1.f / (1.f + expf(-s));
+                    }
+                }
+            }
+            // (no arrive here: the next tile's tail pack follows and arrives once for both)
+            tc_fence_before();
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+}  // namespace dexgg
+
+// ------------------------------------------------------------------------------------------------ host side
+#include <vector>
+
+namespace dexgg {
+
+static size_t ch_data_bytes(int kind, int n_blocks, const int* has_x) {
+    size_t n = 0;
+    for (int b = 0; b < n_blocks; ++b) n += (size_t)ch_block_tiles(has_x[b]) * CH_SLOT_BYTES;
+    return n + (size_t)CH_HEAD_TILES * ch_head_rows(kind) * 128;
+}
+static int ch_total_tiles(int n_blocks, const int* has_x) {
+    int n = CH_HEAD_TILES;
+    for (int b = 0; b < n_blocks; ++b) n += ch_block_tiles(has_x[b]);
+    return n;
+}
+
+size_t chain_stream_bytes(int kind, int n_blocks, const int* has_x) {
+    return align_up(ch_data_bytes(kind, n_blocks, has_x), 256) + align_up((size_t)ch_total_tiles(n_blocks, has_x) * sizeof(ChTile), 256);
+}
+
+// X k-block i of a block's first layer -> source columns (slots 0..3 hold X[256:512], slots 4..7 hold X[0:256])
+static inline int ch_xcol(int i) { return i < 4 ? 256 + 64 * i : 64 * (i - 4); }
+
+int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
+    DEXGG_REQUIRE(s.tailw == 16 && (s.kind == DEXGG_NET_GENERATOR || s.kind == DEXGG_NET_EVALUATOR) && s.n_blocks <= CH_MAX_BLOCKS,
+                  "chain_pack: unsupported network for the fused kernel");
+    std::vector<ChTile> tiles;
+    uint64_t off = 0;
+    auto push = [&](const float* src, int ld, int row0, int nrows, int col0, int mode, int tile_rows) {
+        ChTile t;
+        t.src = src; t.ld = ld; t.row0 = row0; t.nrows = nrows; t.col0 = col0; t.mode = mode; t.tile_rows = tile_rows; t.pad = 0;
+        t.dst_off = off;
+        off += (uint64_t)tile_rows * 128;
+        tiles.push_back(t);
+    };
+    for (int b = 0; b < s.n_blocks; ++b) {
+        const int nkb = s.has_x[b] ? 9 : 1, KT = s.KT[b];
+        auto first_layer = [&](int row_base, int nq) {
+            for (int i = 0; i < nkb; ++i) {
+                const bool tail = (i == nkb - 1);
+                const int col0 = tail ? (s.has_x[b] ? 512 : 0) : ch_xcol(i);
+                for (int q = 0; q < nq; ++q) push(s.Wt[b], KT, row_base + q * 128, 128, col0, tail ? 1 : 0, 128);
+            }
+        };
+        first_layer(256, 4);  // fc3 rows 256..767
+        first_layer(0, 2);    // fc1 rows 0..255
+        for (int h = 0; h < 2; ++h)
+            for (int kb = 0; kb < 4; ++kb)
+                for (int q = 0; q < 2; ++q) push(s.W2[b], 256, h * 256 + q * 128, 128, kb * 64, 0, 128);
+    }
+    const int hr = ch_head_rows(s.kind);
+    for (int i = 0; i < CH_HEAD_TILES; ++i) {
+        if (s.kind == DEXGG_NET_GENERATOR) push(s.Wh, 512, 0, s.nh, ch_xcol(i), 0, hr);
+        else push(s.Wh, 512, 0, 1, ch_xcol(i), 2, hr);
+    }
+    const int has_x[CH_MAX_BLOCKS] = {s.has_x[0], s.has_x[1], s.has_x[2]};
+    DEXGG_REQUIRE(off == ch_data_bytes(s.kind, s.n_blocks, has_x) && (int)tiles.size() == ch_total_tiles(s.n_blocks, has_x),
+                  "chain_pack: internal size mismatch");
+    unsigned char* base = reinterpret_cast<unsigned char*>(stream);
+    ChTile* table = reinterpret_cast<ChTile*>(base + align_up((size_t)off, 256));
+    DEXGG_CUDA_OK(cudaMemcpyAsync(table, tiles.data(), tiles.size() * sizeof(ChTile), cudaMemcpyHostToDevice, st));
+    chain_pack_kernel<<<(unsigned)tiles.size(), 256, 0, st>>>(table, base); count_launches(1);
+    DEXGG_LAUNCH_OK("chain_pack_kernel");
+    return DEXGG_OK;
+}
+
+int chain_forward(const ChainArgs& a, cudaStream_t st) {
+    DEXGG_REQUIRE(a.M >= 1 && a.stream && a.base && a.rows_per_obj >= 1, "chain_forward: bad arguments");
+    static bool attr = false;
+    if (!attr) {
+        DEXGG_CUDA_OK(cudaFuncSetAttribute(chain_umma_kernel<DEXGG_NET_GENERATOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_BYTES));
+        DEXGG_CUDA_OK(cudaFuncSetAttribute(chain_umma_kernel<DEXGG_NET_EVALUATOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_BYTES));
+        attr = true;
+    }
+    const int64_t ntiles = (a.M + 127) / 128;
+    const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
+    if (a.kind == DEXGG_NET_GENERATOR) {
+        DEXGG_REQUIRE(a.z && a.rot && a.transl && a.joint && a.zD >= 1 && a.zD <= 16 && a.nh <= 32 && a.nJ + 9 == a.nh, "chain_forward: bad generator arguments");
+        chain_umma_kernel<DEXGG_NET_GENERATOR><<<grid, CH_THREADS, CH_SMEM_BYTES, st>>>(a);
+    } else {
+        DEXGG_REQUIRE(a.kind == DEXGG_NET_EVALUATOR && a.in_rot && a.in_transl && a.tail_a && a.tail_c && a.p, "chain_forward: bad evaluator arguments");
+        chain_umma_kernel<DEXGG_NET_EVALUATOR><<<grid, CH_THREADS, CH_SMEM_BYTES, st>>>(a);
+    }
+    count_launches(1);
+    DEXGG_LAUNCH_OK("chain_umma_kernel");
+    return DEXGG_OK;
+}
+
+}  // namespace dexgg

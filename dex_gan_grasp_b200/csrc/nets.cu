@@ -16,7 +16,9 @@
 // (discriminator), zero-padded to tailw = 16 or 32 columns.
 #include <cuda_bf16.h>
 
+#include "chain.cuh"
 #include "linear.cuh"
+#include <stdlib.h>
 
 #include <new>
 
@@ -249,6 +251,9 @@ struct dexgg_net {
     // bb_raw [nbase] raw biases, Wh16 [32,512] generator heads
     __nv_bfloat16 *Wb16, *Wh16;
     float* bb_raw;
+    // bf16 mode, generator / evaluator: pre-swizzled weight tile stream of the fused whole-network kernel (chain_umma.cu)
+    __nv_bfloat16* chain_stream;
+    int chain_ok;
     void* arena;
     size_t arena_bytes;
 };
@@ -340,6 +345,17 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
         pack_cols_bf16_kernel<<<nblk((int64_t)n->nh * HID), 256, 0, st>>>(n->Wh16, HID, 0, n->Wh, HID, 0, HID, n->nh); ::dexgg::count_launches(1);
     }
     DEXGG_LAUNCH_OK("net packing kernels");
+    if (n->chain_ok) {
+        ChainPackSrc cs;
+        cs.kind = n->kind; cs.n_blocks = n->n_blocks; cs.tailw = n->tailw; cs.nh = n->nh; cs.Wh = n->Wh;
+        for (int b = 0; b < CH_MAX_BLOCKS; ++b) {
+            const bool on = b < n->n_blocks;
+            cs.Wt[b] = on ? n->blk[b].Wt : nullptr; cs.KT[b] = on ? n->blk[b].KT : 0;
+            cs.has_x[b] = on ? n->blk[b].has_x : 0; cs.W2[b] = on ? n->blk[b].W2 : nullptr;
+        }
+        int rc = chain_pack(cs, n->chain_stream, st);
+        if (rc) return rc;
+    }
     return DEXGG_OK;
 }
 
@@ -389,6 +405,38 @@ void carve_net(dexgg_net* n, Carver& c) {
         n->Wh16 = c.take<__nv_bfloat16>((size_t)32 * HID);
         n->bb_raw = c.take<float>(n->nbase);
     }
+    n->chain_stream = nullptr;
+    n->chain_ok = 0;
+    if (n->precision == DEXGG_PRECISION_BF16 && n->kind != DEXGG_NET_DISCRIMINATOR && n->tailw == 16) {
+        int hx[CH_MAX_BLOCKS] = {0, 0, 0};
+        for (int b = 0; b < n->n_blocks; ++b) hx[b] = n->blk[b].has_x;
+        n->chain_stream = c.take<__nv_bfloat16>(chain_stream_bytes(n->kind, n->n_blocks, hx) / 2);
+        n->chain_ok = 1;
+    }
+}
+
+// DEXGG_NO_CHAIN=1 forces the layer-by-layer tensor-core path (A/B measurements, cross-checks)
+bool chain_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("DEXGG_NO_CHAIN");
+        v = (e && e[0] == '1') ? 0 : 1;
+    }
+    return v == 1;
+}
+
+void chain_common(const dexgg_net* n, ChainArgs& a, const float* base, int64_t n_obj, int64_t rows_per_obj, int64_t M) {
+    a.kind = n->kind; a.n_blocks = n->n_blocks; a.nJ = n->nJ; a.nh = n->nh;
+    a.stream = n->chain_stream;
+    for (int b = 0; b < CH_MAX_BLOCKS; ++b) {
+        const bool on = b < n->n_blocks;
+        a.has_x[b] = on ? n->blk[b].has_x : 0;
+        a.sc[b] = on ? n->blk[b].sc : nullptr; a.sh[b] = on ? n->blk[b].sh : nullptr;
+        a.sc2[b] = on ? n->blk[b].sc2 : nullptr; a.sh2[b] = on ? n->blk[b].sh2 : nullptr;
+    }
+    a.base = base; a.n_obj = n_obj; a.rows_per_obj = rows_per_obj; a.M = M; a.bh = n->bh;
+    a.z = nullptr; a.zD = n->latentD; a.z_offset = 0.f; a.rot = a.transl = a.joint = a.rot6d = nullptr;
+    a.in_rot = a.in_transl = nullptr; a.tail_a = n->tail_a; a.tail_c = n->tail_c; a.p = nullptr;
 }
 
 // workspace of one forward call.  Activations are fp32 (CUDA-core mode) or bf16 (tensor-core mode); `es` is the element
@@ -571,6 +619,12 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
     if ((rc = compute_base(net, bps, n_obj, w, st))) return rc;
     const int zD = net->latentD;
     const bool b16 = net->precision == DEXGG_PRECISION_BF16;
+    if (net->chain_ok && chain_enabled()) {
+        ChainArgs a;
+        chain_common(net, a, w.base, n_obj, rows_per_obj, M);
+        a.z = z; a.z_offset = z_offset; a.rot = rot; a.transl = transl; a.joint = joint; a.rot6d = rot6d;
+        return chain_forward(a, st);
+    }
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
         pack_tail(net, w, z + r0 * zD, zD, nullptr, 0, nullptr, 0, false, mc, w.tail, w.tw, w.XT0 + HID * w.es, w.ldx, nullptr, 0, st);
@@ -610,6 +664,12 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
     const int nJ = net->nJ;
     const bool disc = kind == DEXGG_NET_DISCRIMINATOR;
     const bool b16 = net->precision == DEXGG_PRECISION_BF16;
+    if (net->chain_ok && chain_enabled()) {
+        ChainArgs a;
+        chain_common(net, a, w.base, n_obj, rows_per_obj, M);
+        a.in_rot = rot; a.in_transl = transl; a.p = p;
+        return chain_forward(a, st);
+    }
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
         pack_tail(net, w, rot + r0 * 9, 9, transl + r0 * 3, 3, disc ? joint + r0 * nJ : nullptr, disc ? nJ : 0, true, mc, w.tail, w.tw,
