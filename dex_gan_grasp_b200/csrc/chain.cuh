@@ -24,6 +24,8 @@ struct ChainPackSrc {          // fp32 packed weights of nets.cu (device pointer
     int KT[CH_MAX_BLOCKS];
     int has_x[CH_MAX_BLOCKS];
     const float* W2[CH_MAX_BLOCKS];  // [512, 256]
+    const float* sc[CH_MAX_BLOCKS];  // [768] first-layer affine scale (bn1 on the fc1 rows, 1 on the fc3 rows): folded into Wt
+    const float* sc2[CH_MAX_BLOCKS]; // [512] bn2 scale: folded into W2
     const float* Wh;                 // [nh, 512]
 };
 
@@ -31,11 +33,9 @@ struct ChainArgs {
     int kind, n_blocks, nJ, nh;
     const __nv_bfloat16* stream;     // weight tile stream built by chain_pack
     int has_x[CH_MAX_BLOCKS];
-    const float* sc[CH_MAX_BLOCKS];  // [768] affine of the first layer (bn1 on the fc1 rows, identity on the fc3 rows)
-    const float* sh[CH_MAX_BLOCKS];
-    const float* sc2[CH_MAX_BLOCKS];  // [512] bn2 affine (fc2 bias folded)
-    const float* sh2[CH_MAX_BLOCKS];
-    const float* base;               // [n_obj, 768 * n_blocks] per-object hoisted projection
+    const float* sh2[CH_MAX_BLOCKS];  // [512] bn2 shift (fc2 bias folded); the bn1 / bn2 scales live in the weight stream
+    const float* base;               // [n_obj, 768 * n_blocks] per-object hoisted projection WITH the first-layer affine
+                                     // applied (sc * (bps.W + b) + sh)
     int64_t n_obj, rows_per_obj, M;
     const float* bh;                 // head bias
     // generator

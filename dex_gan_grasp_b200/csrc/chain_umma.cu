@@ -12,8 +12,8 @@
 //   P1  D[0,512)   = [X|t] . W3^T                         fc3 (skip branch), 4 x N=128
 //   E1  R = bf16(lrelu(D + base3)) packed two per column into TMEM [0,128) and [256,384)
 //   P2  D[128,256) , D[384,512) = [X|t] . W1^T            fc1, 2 x N=128
-//   E2  H = bf16(lrelu(sc*(D + base1) + sh)) -> slots 0..3 (X is dead now)
-//   P3  D[128,256) , D[384,512) = H . W2[0:256]^T ;  E3  Xout[:, 0:256]  = bf16(lrelu(R + sc2*D + sh2)) -> slots 4..7
+//   E2  H = bf16(lrelu(D + base1)) -> slots 0..3 (X is dead now; bn1 is folded into W1 and base1)
+//   P3  D[128,256) , D[384,512) = H . W2[0:256]^T ;  E3  Xout[:, 0:256]  = bf16(lrelu(R + D + sh2)) -> slots 4..7 (bn2 scale folded into W2)
 //   P4  same for W2[256:512]                        ;  E4  Xout[:, 256:512] -> slots 0..3 (H is dead now)
 // so every block leaves X columns 0..255 in slots 4..7 and columns 256..511 in slots 0..3; the stream is packed in that
 // k-block order.  Heads: one N=32 (generator) / N=16 (evaluator, weight as hi+lo rows) MMA chain over the 8 X slots, then
@@ -23,11 +23,11 @@
 
 namespace dexgg {
 
-constexpr int CH_SLOT_BYTES = 16384, CH_NSLOT = 9, CH_STAGES = 5, CH_THREADS = 320, CH_HEAD_TILES = 8;
+constexpr int CH_SLOT_BYTES = 16384, CH_NSLOT = 9, CH_STAGES = 4, CH_THREADS = 320, CH_HEAD_TILES = 8;
+constexpr int CH_PARAM_FLOATS = 2 * 768 + 512;  // per block: hoisted base of the tile's (at most) two objects + sh2
 constexpr int CH_A_BYTES = CH_NSLOT * CH_SLOT_BYTES;
-constexpr int CH_SMEM_BYTES = CH_A_BYTES + CH_STAGES * CH_SLOT_BYTES + 256 + 1024;
+constexpr int CH_SMEM_BYTES = CH_A_BYTES + CH_STAGES * CH_SLOT_BYTES + CH_PARAM_FLOATS * 4 + 256 + 1024;
 constexpr int CH_TAIL_SLOT = 8;
-#define CH_LRELU(v) ((v) > 0.f ? (v) : 0.2f * (v))
 
 __host__ __device__ inline int ch_block_tiles(int has_x) { return has_x ? 70 : 22; }  // fc3 4/kb + fc1 2/kb + fc2 16
 __host__ __device__ inline int ch_head_rows(int kind) { return kind == DEXGG_NET_GENERATOR ? 32 : 16; }
@@ -35,6 +35,7 @@ __host__ __device__ inline int ch_head_rows(int kind) { return kind == DEXGG_NET
 // ---------------------------------------------------------------- weight stream packing
 struct ChTile {
     const float* src;   // source matrix (fp32, row-major)
+    const float* rowscale;  // optional per-source-row scale folded in before the bf16 rounding (BatchNorm affine)
     int ld, row0, nrows;  // rows [row0, row0 + nrows) are real, the rest of the tile is zero
     int col0;           // first source column
     int mode;           // 0: 64 plain columns; 1: tail [hi16|hi16|lo16|0]; 2: evaluator head (row 0 = hi, row 8 = lo)
@@ -62,6 +63,7 @@ __global__ void chain_pack_kernel(const ChTile* __restrict__ tiles, unsigned cha
                 lo = r == 8;
             }
         }
+        if (t.rowscale && r < t.nrows) v *= t.rowscale[t.row0 + r];
         __nv_bfloat16 hi = __float2bfloat16_rn(v);
         if (lo) hi = __float2bfloat16_rn(v - __bfloat162float(hi));
         const uint64_t off = t.dst_off + (uint64_t)r * 128 + (uint64_t)((((c >> 3) ^ (r & 7)) << 4) + ((c & 7) << 1));
@@ -119,6 +121,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
     uint64_t* mma_bar = bars + 2 * CH_STAGES; // MMA phase complete -> epilogue
     uint64_t* epi_bar = mma_bar + 1;          // epilogue phase complete (8 warps) -> MMA issuer
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(epi_bar + 1);
+    float* s_par = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(bars) + 256);  // [CH_PARAM_FLOATS]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ntiles = (int)((a.M + 127) / 128);
@@ -207,8 +210,11 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
         // ===================== epilogue warps =====================
         const int quarter = warp & 3, half = (warp - 2) >> 2;
         const int row = quarter * 32 + lane;
+        const int etid = threadIdx.x - 64;  // 0..255 among the epilogue threads
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const int64_t ldbase = 768 * (int64_t)a.n_blocks;
+        float* s_base = s_par;               // [2][768] hoisted base of the tile's first / second object
+        float* s_sh2 = s_par + 2 * 768;      // [512]
         int mphase = 0;
         auto wait_mma = [&]() {
             mbar_wait(mma_bar, mphase);
@@ -221,10 +227,16 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             __syncwarp();
             if (lane == 0) mbar_arrive(epi_bar);
         };
+        auto epi_sync = [&]() { asm volatile("bar.sync 1, 256;" ::: "memory"); };
         for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
             const int64_t m = (int64_t)t * 128 + row;
             const int64_t mm = m < a.M ? m : a.M - 1;
-            const float* base_obj = a.base + (mm / a.rows_per_obj) * ldbase;
+            const int64_t obj = mm / a.rows_per_obj;
+            const int64_t obj0 = ((int64_t)t * 128) / a.rows_per_obj;
+            const int64_t m_last = ((int64_t)t * 128 + 127 < a.M) ? (int64_t)t * 128 + 127 : a.M - 1;
+            const bool staged = (m_last / a.rows_per_obj) - obj0 <= 1;  // the tile touches at most two objects
+            const int64_t obj1 = obj0 + 1 < a.n_obj ? obj0 + 1 : obj0;
+            const float* base_obj = a.base + obj * ldbase;
             // ---- tail k-block (slot 8): per-row inputs as [hi16 | lo16 | hi16 | 0] ----
             if (half == 0) {
                 float v[16];
@@ -255,73 +267,86 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             }
             arrive_epi();
             for (int b = 0; b < a.n_blocks; ++b) {
-                const float* base_b = base_obj + b * 768;
+                // ---- stage this block's per-object base rows and sh2 in shared memory (while the fc3 MMAs run) ----
+                epi_sync();  // every epilogue warp is done with the previous block's parameters
+                if (staged) {
+                    const float* g0 = a.base + obj0 * ldbase + b * 768;
+                    const float* g1 = a.base + obj1 * ldbase + b * 768;
+                    for (int i = etid; i < 768 / 4; i += 256) {
+                        reinterpret_cast<float4*>(s_base)[i] = __ldg(reinterpret_cast<const float4*>(g0) + i);
+                        reinterpret_cast<float4*>(s_base + 768)[i] = __ldg(reinterpret_cast<const float4*>(g1) + i);
+                    }
+                }
+                if (etid < 128) reinterpret_cast<float4*>(s_sh2)[etid] = __ldg(reinterpret_cast<const float4*>(a.sh2[b]) + etid);
+                epi_sync();
+                const float* base_b = staged ? s_base + (obj - obj0) * 768 : base_obj + b * 768;
                 // ---- E1: skip branch R = bf16(lrelu(fc3 + base)), packed in place into TMEM ----
                 wait_mma();
-#pragma unroll 1
+#pragma unroll 2
                 for (int c = 0; c < 8; ++c) {
                     uint32_t r[32];
                     tmem_ld_32x32(tlane + half * 256 + c * 32, r);
-                    tmem_ld_wait();
                     const float* bp = base_b + 256 + half * 256 + c * 32;
+                    float4 bv[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) bv[j] = *reinterpret_cast<const float4*>(bp + 4 * j);
+                    tmem_ld_wait();
                     uint32_t o[16];
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4) {
-                        const float4 bv = *reinterpret_cast<const float4*>(bp + j);
-                        float x0 = __uint_as_float(r[j]) + bv.x, x1 = __uint_as_float(r[j + 1]) + bv.y;
-                        float x2 = __uint_as_float(r[j + 2]) + bv.z, x3 = __uint_as_float(r[j + 3]) + bv.w;
-                        o[j / 2] = pack_bf16x2(CH_LRELU(x0), CH_LRELU(x1));
-                        o[j / 2 + 1] = pack_bf16x2(CH_LRELU(x2), CH_LRELU(x3));
+                    for (int j = 0; j < 8; ++j) {
+                        const float x0 = __uint_as_float(r[4 * j]) + bv[j].x, x1 = __uint_as_float(r[4 * j + 1]) + bv[j].y;
+                        const float x2 = __uint_as_float(r[4 * j + 2]) + bv[j].z, x3 = __uint_as_float(r[4 * j + 3]) + bv[j].w;
+                        o[2 * j] = pack_bf16x2(fmaxf(x0, 0.2f * x0), fmaxf(x1, 0.2f * x1));
+                        o[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.2f * x2), fmaxf(x3, 0.2f * x3));
                     }
                     tmem_st_32x16(tlane + half * 256 + c * 16, o);
                 }
                 tmem_st_wait();
                 arrive_epi();
-                // ---- E2: H = bf16(lrelu(sc * (fc1 + base) + sh)) -> slots 0..3 ----
+                // ---- E2: H = bf16(lrelu(fc1 + base)) -> slots 0..3 (bn1 is folded into the weights and the base) ----
                 wait_mma();
-                {
-                    const float* sc = a.sc[b];
-                    const float* sh = a.sh[b];
-#pragma unroll 1
-                    for (int c = 0; c < 4; ++c) {
-                        uint32_t r[32];
-                        tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
-                        tmem_ld_wait();
-                        const int n0 = half * 128 + c * 32;
-                        float v[32];
+#pragma unroll 2
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
+                    const int n0 = half * 128 + c * 32;
+                    float4 bv[8];
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            const float4 bv = *reinterpret_cast<const float4*>(base_b + n0 + j);
-                            const float4 s4 = __ldg(reinterpret_cast<const float4*>(sc + n0 + j));
-                            const float4 h4 = __ldg(reinterpret_cast<const float4*>(sh + n0 + j));
-                            float x0 = fmaf(__uint_as_float(r[j]) + bv.x, s4.x, h4.x), x1 = fmaf(__uint_as_float(r[j + 1]) + bv.y, s4.y, h4.y);
-                            float x2 = fmaf(__uint_as_float(r[j + 2]) + bv.z, s4.z, h4.z), x3 = fmaf(__uint_as_float(r[j + 3]) + bv.w, s4.w, h4.w);
-                            v[j] = CH_LRELU(x0); v[j + 1] = CH_LRELU(x1); v[j + 2] = CH_LRELU(x2); v[j + 3] = CH_LRELU(x3);
-                        }
-                        store_row32(sA + (half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
+                    for (int j = 0; j < 8; ++j) bv[j] = *reinterpret_cast<const float4*>(base_b + n0 + 4 * j);
+                    tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float x0 = __uint_as_float(r[4 * j]) + bv[j].x, x1 = __uint_as_float(r[4 * j + 1]) + bv[j].y;
+                        const float x2 = __uint_as_float(r[4 * j + 2]) + bv[j].z, x3 = __uint_as_float(r[4 * j + 3]) + bv[j].w;
+                        v[4 * j] = fmaxf(x0, 0.2f * x0); v[4 * j + 1] = fmaxf(x1, 0.2f * x1);
+                        v[4 * j + 2] = fmaxf(x2, 0.2f * x2); v[4 * j + 3] = fmaxf(x3, 0.2f * x3);
                     }
+                    store_row32(sA + (half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
                 }
                 arrive_epi();
-                // ---- E3 / E4: Xout = bf16(lrelu(R + sc2 * fc2 + sh2)) -> slots 4..7 (h = 0) / 0..3 (h = 1) ----
+                // ---- E3 / E4: Xout = bf16(lrelu(R + fc2 + sh2)) -> slots 4..7 (h = 0) / 0..3 (h = 1) ----
                 for (int h = 0; h < 2; ++h) {
                     wait_mma();
-                    const float* sc2 = a.sc2[b];
-                    const float* sh2 = a.sh2[b];
-#pragma unroll 1
+#pragma unroll 2
                     for (int c = 0; c < 4; ++c) {
                         uint32_t r[32], rr[16];
                         tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
                         tmem_ld_32x16(tlane + h * 256 + half * 64 + c * 16, rr);
-                        tmem_ld_wait();
                         const int n0 = h * 256 + half * 128 + c * 32;
+                        float4 hv[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) hv[j] = *reinterpret_cast<const float4*>(s_sh2 + n0 + 4 * j);
+                        tmem_ld_wait();
                         float v[32];
 #pragma unroll
-                        for (int j = 0; j < 32; j += 2) {
-                            const float2 s2 = __ldg(reinterpret_cast<const float2*>(sc2 + n0 + j));
-                            const float2 h2 = __ldg(reinterpret_cast<const float2*>(sh2 + n0 + j));
-                            float x0 = fmaf(__uint_as_float(r[j]), s2.x, h2.x) + bf16_lo(rr[j / 2]);
-                            float x1 = fmaf(__uint_as_float(r[j + 1]), s2.y, h2.y) + bf16_hi(rr[j / 2]);
-                            v[j] = CH_LRELU(x0); v[j + 1] = CH_LRELU(x1);
+                        for (int j = 0; j < 8; ++j) {
+                            const float x0 = __uint_as_float(r[4 * j]) + hv[j].x + bf16_lo(rr[2 * j]);
+                            const float x1 = __uint_as_float(r[4 * j + 1]) + hv[j].y + bf16_hi(rr[2 * j]);
+                            const float x2 = __uint_as_float(r[4 * j + 2]) + hv[j].z + bf16_lo(rr[2 * j + 1]);
+                            const float x3 = __uint_as_float(r[4 * j + 3]) + hv[j].w + bf16_hi(rr[2 * j + 1]);
+                            v[4 * j] = fmaxf(x0, 0.2f * x0); v[4 * j + 1] = fmaxf(x1, 0.2f * x1);
+                            v[4 * j + 2] = fmaxf(x2, 0.2f * x2); v[4 * j + 3] = fmaxf(x3, 0.2f * x3);
                         }
                         store_row32(sA + ((h ? 0 : 4) + half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
                     }
@@ -420,8 +445,9 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
                   "chain_pack: unsupported network for the fused kernel");
     std::vector<ChTile> tiles;
     uint64_t off = 0;
-    auto push = [&](const float* src, int ld, int row0, int nrows, int col0, int mode, int tile_rows) {
+    auto push = [&](const float* src, int ld, int row0, int nrows, int col0, int mode, int tile_rows, const float* rowscale = nullptr) {
         ChTile t;
+        t.rowscale = rowscale;
         t.src = src; t.ld = ld; t.row0 = row0; t.nrows = nrows; t.col0 = col0; t.mode = mode; t.tile_rows = tile_rows; t.pad = 0;
         t.dst_off = off;
         off += (uint64_t)tile_rows * 128;
@@ -433,14 +459,14 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
             for (int i = 0; i < nkb; ++i) {
                 const bool tail = (i == nkb - 1);
                 const int col0 = tail ? (s.has_x[b] ? 512 : 0) : ch_xcol(i);
-                for (int q = 0; q < nq; ++q) push(s.Wt[b], KT, row_base + q * 128, 128, col0, tail ? 1 : 0, 128);
+                for (int q = 0; q < nq; ++q) push(s.Wt[b], KT, row_base + q * 128, 128, col0, tail ? 1 : 0, 128, s.sc[b]);
             }
         };
         first_layer(256, 4);  // fc3 rows 256..767
         first_layer(0, 2);    // fc1 rows 0..255
         for (int h = 0; h < 2; ++h)
             for (int kb = 0; kb < 4; ++kb)
-                for (int q = 0; q < 2; ++q) push(s.W2[b], 256, h * 256 + q * 128, 128, kb * 64, 0, 128);
+                for (int q = 0; q < 2; ++q) push(s.W2[b], 256, h * 256 + q * 128, 128, kb * 64, 0, 128, s.sc2[b]);
     }
     const int hr = ch_head_rows(s.kind);
     for (int i = 0; i < CH_HEAD_TILES; ++i) {

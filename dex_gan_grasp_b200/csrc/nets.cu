@@ -253,6 +253,7 @@ struct dexgg_net {
     float* bb_raw;
     // bf16 mode, generator / evaluator: pre-swizzled weight tile stream of the fused whole-network kernel (chain_umma.cu)
     __nv_bfloat16* chain_stream;
+    float *chain_sc, *chain_sh;  // [nbase] first-layer affine of every block, applied to the hoisted base by compute_base
     int chain_ok;
     void* arena;
     size_t arena_bytes;
@@ -352,6 +353,11 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
             const bool on = b < n->n_blocks;
             cs.Wt[b] = on ? n->blk[b].Wt : nullptr; cs.KT[b] = on ? n->blk[b].KT : 0;
             cs.has_x[b] = on ? n->blk[b].has_x : 0; cs.W2[b] = on ? n->blk[b].W2 : nullptr;
+            cs.sc[b] = on ? n->blk[b].sc : nullptr; cs.sc2[b] = on ? n->blk[b].sc2 : nullptr;
+            if (on) {
+                DEXGG_CUDA_OK(cudaMemcpyAsync(n->chain_sc + b * NCAT, n->blk[b].sc, NCAT * 4, cudaMemcpyDeviceToDevice, st));
+                DEXGG_CUDA_OK(cudaMemcpyAsync(n->chain_sh + b * NCAT, n->blk[b].sh, NCAT * 4, cudaMemcpyDeviceToDevice, st));
+            }
         }
         int rc = chain_pack(cs, n->chain_stream, st);
         if (rc) return rc;
@@ -406,11 +412,14 @@ void carve_net(dexgg_net* n, Carver& c) {
         n->bb_raw = c.take<float>(n->nbase);
     }
     n->chain_stream = nullptr;
+    n->chain_sc = n->chain_sh = nullptr;
     n->chain_ok = 0;
     if (n->precision == DEXGG_PRECISION_BF16 && n->kind != DEXGG_NET_DISCRIMINATOR && n->tailw == 16) {
         int hx[CH_MAX_BLOCKS] = {0, 0, 0};
         for (int b = 0; b < n->n_blocks; ++b) hx[b] = n->blk[b].has_x;
         n->chain_stream = c.take<__nv_bfloat16>(chain_stream_bytes(n->kind, n->n_blocks, hx) / 2);
+        n->chain_sc = c.take<float>(n->nbase);
+        n->chain_sh = c.take<float>(n->nbase);
         n->chain_ok = 1;
     }
 }
@@ -431,8 +440,7 @@ void chain_common(const dexgg_net* n, ChainArgs& a, const float* base, int64_t n
     for (int b = 0; b < CH_MAX_BLOCKS; ++b) {
         const bool on = b < n->n_blocks;
         a.has_x[b] = on ? n->blk[b].has_x : 0;
-        a.sc[b] = on ? n->blk[b].sc : nullptr; a.sh[b] = on ? n->blk[b].sh : nullptr;
-        a.sc2[b] = on ? n->blk[b].sc2 : nullptr; a.sh2[b] = on ? n->blk[b].sh2 : nullptr;
+        a.sh2[b] = on ? n->blk[b].sh2 : nullptr;
     }
     a.base = base; a.n_obj = n_obj; a.rows_per_obj = rows_per_obj; a.M = M; a.bh = n->bh;
     a.z = nullptr; a.zD = n->latentD; a.z_offset = 0.f; a.rot = a.transl = a.joint = a.rot6d = nullptr;
@@ -486,13 +494,14 @@ int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int6
 }
 
 // base[n_obj, nbase] = bn(bps) · W_bpsᵀ + bias    (once per object; for row-wise inputs n_obj == M)
-int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, const FwdWs& w, cudaStream_t st) {
+int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, const FwdWs& w, cudaStream_t st, bool chain = false) {
     if (n->precision == DEXGG_PRECISION_BF16) {
         bps_bn_split_kernel<<<nblk(n_obj * IN_BPS), 256, 0, st>>>(bps, n->in_a, n->in_c, w.Ab16, n_obj); ::dexgg::count_launches(1);
         LinearB16 q;
         q.A = w.Ab16; q.lda = 3 * IN_BPS; q.W = n->Wb16; q.ldw = 3 * IN_BPS;
         q.M = (int)n_obj; q.N = n->nbase; q.K = 3 * IN_BPS; q.C32 = w.base; q.ldc = n->nbase;
         q.ep.bias = n->bb_raw;
+        if (chain) { q.ep.scale = n->chain_sc; q.ep.shift = n->chain_sh; }  // base' = sc * (bps.W + b) + sh
         return linear_bf16(q, st);
     }
     LinearF32 p;
@@ -616,10 +625,11 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     FwdWs w;
     carve_ws(net, M, n_obj, workspace, w);
-    if ((rc = compute_base(net, bps, n_obj, w, st))) return rc;
+    const bool use_chain = net->chain_ok && chain_enabled();
+    if ((rc = compute_base(net, bps, n_obj, w, st, use_chain))) return rc;
     const int zD = net->latentD;
     const bool b16 = net->precision == DEXGG_PRECISION_BF16;
-    if (net->chain_ok && chain_enabled()) {
+    if (use_chain) {
         ChainArgs a;
         chain_common(net, a, w.base, n_obj, rows_per_obj, M);
         a.z = z; a.z_offset = z_offset; a.rot = rot; a.transl = transl; a.joint = joint; a.rot6d = rot6d;
@@ -660,11 +670,12 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     FwdWs w;
     carve_ws(net, M, n_obj, workspace, w);
-    if ((rc = compute_base(net, bps, n_obj, w, st))) return rc;
+    const bool use_chain = net->chain_ok && chain_enabled();
+    if ((rc = compute_base(net, bps, n_obj, w, st, use_chain))) return rc;
     const int nJ = net->nJ;
     const bool disc = kind == DEXGG_NET_DISCRIMINATOR;
     const bool b16 = net->precision == DEXGG_PRECISION_BF16;
-    if (net->chain_ok && chain_enabled()) {
+    if (use_chain) {
         ChainArgs a;
         chain_common(net, a, w.base, n_obj, rows_per_obj, M);
         a.in_rot = rot; a.in_transl = transl; a.p = p;
