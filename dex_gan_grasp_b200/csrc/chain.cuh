@@ -47,6 +47,8 @@ struct ChainArgs {
     const float *in_rot, *in_transl; // [M,9], [M,3]
     const float *tail_a, *tail_c;    // input BatchNorm affine of the 12 pose columns
     float* p;                        // [M]
+    long long* debug_clock;          // timing experiment only: [512] clock64 samples of CTA 0 (MMA issuer | epilogue warp)
+    int debug_no_stream;             // timing experiment only (DEXGG_CHAIN_NOSTREAM=1): weights are not loaded
 };
 
 size_t chain_stream_bytes(int kind, int n_blocks, const int* has_x);

@@ -3,17 +3,17 @@
 //
 // One persistent CTA per SM, 320 threads, one 128-grasp tile at a time:
 //   warp 0      weight producer: walks the pre-swizzled weight tile stream (built once by chain_pack) with 1-D bulk TMA
-//               copies into a 5-stage x 16 KB shared-memory ring (mbarrier expect_tx / complete_tx)
-//   warp 1      MMA issuer: one thread issues tcgen05.mma.kind::f16 (M=128, N=128, K=16); A = activation k-blocks resident
+//               copies into a 4-stage x 16 KB shared-memory ring (mbarrier expect_tx / complete_tx)
+//   warp 1      MMA issuer: one thread issues tcgen05.mma.kind::f16 (M=128, N=256, K=16); A = activation k-blocks resident
 //               in shared memory (9 slots x [128 rows x 64 bf16], 128B swizzle), B = ring stage, D = TMEM
 //   warps 2..9  epilogue: tcgen05.ld -> per-object base + BatchNorm affine + LeakyReLU -> bf16 -> next layer's A operand in
 //               shared memory (or packed back into TMEM with tcgen05.st for the residual branch)
 // Per ResBlock (ResBlock.forward, networks.py:43-56), with X the 512-wide input (slots 0..7) and t the tail k-block (slot 8):
-//   P1  D[0,512)   = [X|t] . W3^T                         fc3 (skip branch), 4 x N=128
-//   E1  R = bf16(lrelu(D + base3)) packed two per column into TMEM [0,128) and [256,384)
-//   P2  D[128,256) , D[384,512) = [X|t] . W1^T            fc1, 2 x N=128
+//   P1  D[0,512)   = [X|t] . W3^T                         fc3 (skip branch), 2 x N=256 per k-block
+//   E1  R = bf16(lrelu(D + base3)) packed two per column into TMEM [0,128) and [384,512)
+//   P2  D[128,384) = [X|t] . W1^T                         fc1, N=256
 //   E2  H = bf16(lrelu(D + base1)) -> slots 0..3 (X is dead now; bn1 is folded into W1 and base1)
-//   P3  D[128,256) , D[384,512) = H . W2[0:256]^T ;  E3  Xout[:, 0:256]  = bf16(lrelu(R + D + sh2)) -> slots 4..7 (bn2 scale folded into W2)
+//   P3  D[128,384) = H . W2[0:256]^T ;  E3  Xout[:, 0:256]  = bf16(lrelu(R + D + sh2)) -> slots 4..7 (bn2 scale folded into W2)
 //   P4  same for W2[256:512]                        ;  E4  Xout[:, 256:512] -> slots 0..3 (H is dead now)
 // so every block leaves X columns 0..255 in slots 4..7 and columns 256..511 in slots 0..3; the stream is packed in that
 // k-block order.  Heads: one N=32 (generator) / N=16 (evaluator, weight as hi+lo rows) MMA chain over the 8 X slots, then
@@ -155,8 +155,9 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 for (int i = 0; i < n_main + CH_HEAD_TILES; ++i) {
                     const uint32_t bytes = i < n_main ? (uint32_t)CH_SLOT_BYTES : HEAD_BYTES;
                     mbar_wait(&empty[stage], phase ^ 1);
+                    if (a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
                     mbar_expect_tx(&full[stage], bytes);
-                    bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, bytes, &full[stage]);
+                    bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, bytes, &full[stage]); }
                     off += bytes;
                     if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -165,13 +166,18 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(128, 128), idesc_h = umma_idesc_bf16(128, HEAD_ROWS);
+            const uint32_t idesc256 = umma_idesc_bf16(128, 256), idesc_h = umma_idesc_bf16(128, HEAD_ROWS);
             const uint32_t sA_u = smem_u32(sA), sR_u = smem_u32(sR);
             int stage = 0, phase = 0, ephase = 0;
+            int dbg_n = 0;
+            auto dbg = [&]() {
+                if (a.debug_clock && blockIdx.x == 0 && dbg_n < 256) a.debug_clock[dbg_n++] = clock64();
+            };
             auto wait_epi = [&]() {
                 mbar_wait(epi_bar, ephase);
                 ephase ^= 1;
                 tc_fence_after();
+                dbg();
             };
             auto mma_tile = [&](uint32_t d_col, int slot, uint32_t id, bool first) {
                 mbar_wait(&full[stage], phase);
@@ -183,27 +189,40 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 umma_commit(&empty[stage]);
                 if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
             };
+            // two consecutive 16 KB ring stages (always an even / odd pair: every phase has an even tile count) form one
+            // [256 x 64] B tile: N = 256 halves the shared-memory operand traffic per MAC against N = 128
+            auto mma_tile2 = [&](uint32_t d_col, int slot, bool first) {
+                mbar_wait(&full[stage], phase);
+                mbar_wait(&full[stage + 1], phase);
+                tc_fence_after();
+                const uint64_t ad = umma_desc_sw128_kmajor(sA_u + slot * CH_SLOT_BYTES);
+                const uint64_t bd = umma_desc_sw128_kmajor(sR_u + stage * CH_SLOT_BYTES);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + d_col, ad + 2 * k, bd + 2 * k, idesc256, !(first && k == 0));
+                umma_commit(&empty[stage]);
+                umma_commit(&empty[stage + 1]);
+                stage += 2;
+                if (stage == CH_STAGES) { stage = 0; phase ^= 1; }
+            };
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
                 for (int b = 0; b < a.n_blocks; ++b) {
                     const int nkb = a.has_x[b] ? 9 : 1, s0 = a.has_x[b] ? 0 : CH_TAIL_SLOT;
-                    wait_epi();  // P1: fc3
+                    wait_epi();  // P1: fc3 -> D[0,512)
                     for (int i = 0; i < nkb; ++i)
-                        for (int q = 0; q < 4; ++q) mma_tile(q * 128, s0 + i, idesc, i == 0);
-                    umma_commit(mma_bar);
-                    wait_epi();  // P2: fc1
-                    for (int i = 0; i < nkb; ++i)
-                        for (int q = 0; q < 2; ++q) mma_tile(q ? 384 : 128, s0 + i, idesc, i == 0);
-                    umma_commit(mma_bar);
-                    for (int h = 0; h < 2; ++h) {  // P3 / P4: fc2 halves, A = H in slots 0..3
+                        for (int q = 0; q < 2; ++q) mma_tile2(q * 256, s0 + i, i == 0);
+                    umma_commit(mma_bar); dbg();
+                    wait_epi();  // P2: fc1 -> D[128,384)
+                    for (int i = 0; i < nkb; ++i) mma_tile2(128, s0 + i, i == 0);
+                    umma_commit(mma_bar); dbg();
+                    for (int h = 0; h < 2; ++h) {  // P3 / P4: fc2 halves -> D[128,384), A = H in slots 0..3
                         wait_epi();
-                        for (int kb = 0; kb < 4; ++kb)
-                            for (int q = 0; q < 2; ++q) mma_tile(q ? 384 : 128, kb, idesc, kb == 0);
-                        umma_commit(mma_bar);
+                        for (int kb = 0; kb < 4; ++kb) mma_tile2(128, kb, kb == 0);
+                        umma_commit(mma_bar); dbg();
                     }
                 }
                 wait_epi();  // heads over the 8 X slots
                 for (int s = 0; s < CH_HEAD_TILES; ++s) mma_tile(128, s, idesc_h, s == 0);
-                umma_commit(mma_bar);
+                umma_commit(mma_bar); dbg();
             }
         }
     } else {
@@ -216,12 +235,18 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
         float* s_base = s_par;               // [2][768] hoisted base of the tile's first / second object
         float* s_sh2 = s_par + 2 * 768;      // [512]
         int mphase = 0;
+        int dbg_n = 0;
+        auto dbg = [&]() {
+            if (a.debug_clock && blockIdx.x == 0 && warp == 2 && lane == 0 && dbg_n < 256) a.debug_clock[256 + dbg_n++] = clock64();
+        };
         auto wait_mma = [&]() {
             mbar_wait(mma_bar, mphase);
             mphase ^= 1;
             tc_fence_after();
+            dbg();
         };
         auto arrive_epi = [&]() {
+            dbg();
             tc_fence_before();
             fence_proxy_async();
             __syncwarp();
@@ -283,7 +308,10 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 // ---- E1: skip branch R = bf16(lrelu(fc3 + base)), packed in place into TMEM ----
                 wait_mma();
 #pragma unroll 2
-                for (int c = 0; c < 8; ++c) {
+                for (int cc = 0; cc < 8; ++cc) {
+                    // half 0 packs columns [0,256) upwards into [0,128); half 1 packs [256,512) DOWNWARDS into [384,512): a
+                    // warp only ever overwrites columns it has already read, and [128,384) is left free as one 256-column block
+                    const int c = half ? 7 - cc : cc;
                     uint32_t r[32];
                     tmem_ld_32x32(tlane + half * 256 + c * 32, r);
                     const float* bp = base_b + 256 + half * 256 + c * 32;
@@ -299,7 +327,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                         o[2 * j] = pack_bf16x2(fmaxf(x0, 0.2f * x0), fmaxf(x1, 0.2f * x1));
                         o[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.2f * x2), fmaxf(x3, 0.2f * x3));
                     }
-                    tmem_st_32x16(tlane + half * 256 + c * 16, o);
+                    tmem_st_32x16(tlane + (half ? 384 : 0) + c * 16, o);
                 }
                 tmem_st_wait();
                 arrive_epi();
@@ -308,7 +336,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
 #pragma unroll 2
                 for (int c = 0; c < 4; ++c) {
                     uint32_t r[32];
-                    tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
+                    tmem_ld_32x32(tlane + 128 + half * 128 + c * 32, r);
                     const int n0 = half * 128 + c * 32;
                     float4 bv[8];
 #pragma unroll
@@ -331,8 +359,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
 #pragma unroll 2
                     for (int c = 0; c < 4; ++c) {
                         uint32_t r[32], rr[16];
-                        tmem_ld_32x32(tlane + (half ? 384 : 128) + c * 32, r);
-                        tmem_ld_32x16(tlane + h * 256 + half * 64 + c * 16, rr);
+                        tmem_ld_32x32(tlane + 128 + half * 128 + c * 32, r);
+                        tmem_ld_32x16(tlane + (h ? 384 : 0) + half * 64 + c * 16, rr);
                         const int n0 = h * 256 + half * 128 + c * 32;
                         float4 hv[8];
 #pragma unroll
@@ -418,6 +446,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
 }  // namespace dexgg
 
 // ------------------------------------------------------------------------------------------------ host side
+#include <stdlib.h>
 #include <vector>
 
 namespace dexgg {
@@ -493,6 +522,13 @@ int chain_forward(const ChainArgs& a, cudaStream_t st) {
         attr = true;
     }
     const int64_t ntiles = (a.M + 127) / 128;
+    { const char* e = getenv("DEXGG_CHAIN_NOSTREAM"); const_cast<ChainArgs&>(a).debug_no_stream = (e && e[0] == '1') ? 1 : 0; }
+    static long long* dbg_buf = nullptr;
+    if (getenv("DEXGG_CHAIN_CLOCKS")) {  // timing experiment: dump the phase timeline of CTA 0 after the launch
+        if (!dbg_buf) DEXGG_CUDA_OK(cudaMalloc(&dbg_buf, 512 * sizeof(long long)));
+        DEXGG_CUDA_OK(cudaMemsetAsync(dbg_buf, 0, 512 * sizeof(long long), st));
+        const_cast<ChainArgs&>(a).debug_clock = dbg_buf;
+    }
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
     if (a.kind == DEXGG_NET_GENERATOR) {
         DEXGG_REQUIRE(a.z && a.rot && a.transl && a.joint && a.zD >= 1 && a.zD <= 16 && a.nh <= 32 && a.nJ + 9 == a.nh, "chain_forward: bad generator arguments");
@@ -503,6 +539,20 @@ int chain_forward(const ChainArgs& a, cudaStream_t st) {
     }
     count_launches(1);
     DEXGG_LAUNCH_OK("chain_umma_kernel");
+    if (a.debug_clock) {
+        std::vector<long long> h(512);
+        DEXGG_CUDA_OK(cudaMemcpy(h.data(), dbg_buf, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
+        FILE* f = fopen(getenv("DEXGG_CHAIN_CLOCKS"), "a");
+        if (f) {
+            fprintf(f, "kind %d\n", a.kind);
+            for (int r = 0; r < 2; ++r) {
+                fprintf(f, r ? "epi:" : "mma:");
+                for (int i = 0; i < 256 && h[r * 256 + i]; ++i) fprintf(f, " %lld", h[r * 256 + i] - h[0]);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+    }
     return DEXGG_OK;
 }
 

@@ -445,6 +445,7 @@ void chain_common(const dexgg_net* n, ChainArgs& a, const float* base, int64_t n
     a.base = base; a.n_obj = n_obj; a.rows_per_obj = rows_per_obj; a.M = M; a.bh = n->bh;
     a.z = nullptr; a.zD = n->latentD; a.z_offset = 0.f; a.rot = a.transl = a.joint = a.rot6d = nullptr;
     a.in_rot = a.in_transl = nullptr; a.tail_a = n->tail_a; a.tail_c = n->tail_c; a.p = nullptr;
+    a.debug_clock = nullptr; a.debug_no_stream = 0;
 }
 
 // workspace of one forward call.  Activations are fp32 (CUDA-core mode) or bf16 (tensor-core mode); `es` is the element
