@@ -37,7 +37,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--precision", default=os.environ.get("DEXGG_PRECISION", "fp32"), choices=["fp32", "bf16"])
+    ap.add_argument("--precision", default=os.environ.get("DEXGG_PRECISION", "bf16"), choices=["fp32", "bf16"],
+                    help="MLP arithmetic: bf16 = tcgen05 tensor cores (headline, north_star), fp32 = CUDA-core 1e-4 mode")
+    ap.add_argument("--no-fp32-line", action="store_true", help="skip the secondary fp32-exact-mode measurement")
     ap.add_argument("--clouds", type=int, default=N_CLOUDS)
     ap.add_argument("--samples", type=int, default=N_SAMPLES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -250,9 +252,10 @@ def main():
     bps_pairs = 4096.0 * B * N_POINTS
     bps_lane_tops = 6 * bps_pairs / (t_bps * 1e-3) / 1e12
     if args.precision == "bf16":
-        roof = {"bound": "tensor", "kernel": "linear_umma_kernel (tcgen05 bf16, all MLP layers)", "achieved": mlp_tflops,
+        roof = {"bound": "tensor", "kernel": "chain_umma_kernel<G>,<E> (fused whole-network tcgen05 bf16 kernels; executed-algorithm FLOP of the hoisted chain)", "achieved": mlp_tflops,
                 "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": mlp_tflops / pk["bf16_tflops_sustained"],
-                "peak_source": pk_src + " bf16_tflops_sustained", "traffic": None}
+                "peak_source": pk_src + " bf16_tflops_sustained",
+                "traffic": {"unit": "MB per launch (ncu dram__bytes_read+write, profiles/r01c_chain_ncu_full.md)", "generator": 70.6, "evaluator": 62.2}}
     else:
         roof = {"bound": "fp32", "kernel": "linear_simt_kernel (fp32 CUDA-core mode, all MLP layers)", "achieved": mlp_tflops,
                 "peak": fp32_tflops, "unit": "TFLOP/s", "frac": mlp_tflops / fp32_tflops,
@@ -265,6 +268,26 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max, ms_e2e_max = float(t[0]), float(t[1])
+
+    fp32_line = None
+    if args.precision == "bf16" and not args.no_fp32_line:
+        # secondary: the fp32 CUDA-core mode (1e-4 parity contract) on a quarter of the clouds, same pipeline
+        model32 = DexGanGrasp(dict(cfg, precision="fp32"))
+        model32.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+        model32.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+        pipe32 = GraspPipeline(model32.DexGANGrasp, model32.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025)
+        Bq = max(B // 4, 1)
+        c32, z32 = clouds_d[:Bq].contiguous(), z_d[:Bq * S].contiguous()
+        pipe32.run_device(c32, z32, S)
+        torch.cuda.synchronize()
+        a32, b32 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a32.record()
+        pipe32.run_device(c32, z32, S)
+        b32.record()
+        b32.synchronize()
+        fp32_line = {"value": Bq * S / (a32.elapsed_time(b32) * 1e-3), "unit": "grasps/s per GPU", "ms": a32.elapsed_time(b32),
+                     "sample": f"{Bq} clouds x {S} z", "note": "fp32 CUDA-core MLP mode (within 1e-4 of the reference)"}
+        del model32, pipe32
 
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
@@ -284,7 +307,7 @@ def main():
             "e2e": {"value": world * M / (ms_e2e_max * 1e-3), "unit": "grasps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e_max},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "stages": stages, "cpu_baseline": cpu,
-            "kept_grasps_last_step": kept,
+            "kept_grasps_last_step": kept, "fp32_exact_mode": fp32_line,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

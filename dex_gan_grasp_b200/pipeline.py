@@ -22,6 +22,7 @@ class GraspPipeline:
         self.k, self.thresh, self.z_offset = int(k), float(thresh), float(z_offset)
         self._ws = bps_mod._Workspace()
         self._stage = {}
+        self._copy_stream = None
         gan.eval()
         evaluator.eval()
 
@@ -31,7 +32,7 @@ class GraspPipeline:
         d, _ = bps_mod.bps_encode_device(self.basis, clouds, return_idx=False, ws=self._ws)
         return d
 
-    def run_device(self, clouds, z, samples_per_object):
+    def run_device(self, clouds, z, samples_per_object, z_ready=None):
         """clouds [B,N,3], z [B*S,latentD] on the device.  Returns a dict of device tensors:
         idx [B,k] i32 (global row ids, -1 padded), count [B], score [B,k], rot_matrix [B,k,3,3], transl [B,k,3],
         joint_conf [B,k,nJ] (rows beyond count are zero)."""
@@ -42,6 +43,8 @@ class GraspPipeline:
         L = _native.lib()
         dev = self.device
         enc = self.encode(clouds)
+        if z_ready is not None:
+            torch.cuda.current_stream(dev).wait_event(z_ready)
         rot, transl, joint, _ = self.gan.generator.native_forward(z, enc, self.z_offset, False)
         p = self.eva.native_forward(enc, rot, transl)
         k = min(self.k, S)
@@ -72,9 +75,17 @@ class GraspPipeline:
             self._stage = {key: (torch.empty(clouds_host.shape, dtype=torch.float32, device=dev),
                                  torch.empty(z_host.shape, dtype=torch.float32, device=dev))}
         d_clouds, d_z = self._stage[key]
+        # clouds first (the BPS stage needs only them); the latent batch is copied on a side stream underneath the BPS kernel
+        main = torch.cuda.current_stream(dev)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(dev)
         d_clouds.copy_(clouds_host, non_blocking=True)
-        d_z.copy_(z_host, non_blocking=True)
-        out = self.run_device(d_clouds, d_z, samples_per_object)
+        self._copy_stream.wait_stream(main)  # d_z may still be read by the previous step
+        with torch.cuda.stream(self._copy_stream):
+            d_z.copy_(z_host, non_blocking=True)
+            z_ready = torch.cuda.Event()
+            z_ready.record(self._copy_stream)
+        out = self.run_device(d_clouds, d_z, samples_per_object, z_ready=z_ready)
         B, k = out["idx"].shape
         packed = torch.cat([out["score"].reshape(B, k, 1), out["idx"].float().reshape(B, k, 1), out["rot_matrix"].reshape(B, k, 9),
                             out["transl"], out["joint_conf"]], dim=2)
