@@ -92,6 +92,31 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const uint32_t*>(&h);
 }
+// bf16x2( leaky_relu(acc + add) ) for two adjacent columns: packed fp32x2 add / mul (FADD2, FMUL2), same roundings as scalar
+__device__ __forceinline__ uint32_t lrelu_pack2(uint32_t a0, uint32_t a1, float b0, float b1) {
+    const f32x2 x = add2(pack2(__uint_as_float(a0), __uint_as_float(a1)), pack2(b0, b1));
+    const f32x2 t = mul2(x, pack2(0.2f, 0.2f));
+    float x0, x1, t0, t1;
+    unpack2(x, x0, x1);
+    unpack2(t, t0, t1);
+    return pack_bf16x2(fmaxf(x0, t0), fmaxf(x1, t1));
+}
+// same with a third, bf16x2-packed addend (the residual branch)
+__device__ __forceinline__ uint32_t lrelu_pack3(uint32_t a0, uint32_t a1, float b0, float b1, uint32_t r2) {
+    f32x2 x = add2(pack2(__uint_as_float(a0), __uint_as_float(a1)), pack2(b0, b1));
+    x = add2(x, pack2(__uint_as_float(r2 << 16), __uint_as_float(r2 & 0xffff0000u)));
+    const f32x2 t = mul2(x, pack2(0.2f, 0.2f));
+    float x0, x1, t0, t1;
+    unpack2(x, x0, x1);
+    unpack2(t, t0, t1);
+    return pack_bf16x2(fmaxf(x0, t0), fmaxf(x1, t1));
+}
+// 32 consecutive bf16 columns, already packed in pairs, into an A-operand slot (4 swizzle chunks from chunk `ci0`)
+__device__ __forceinline__ void store_row32p(unsigned char* slot, int row, int ci0, const uint32_t (&o)[16]) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        *reinterpret_cast<uint4*>(slot + row * 128 + (((ci0 + q) ^ (row & 7)) << 4)) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+}
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 // 32 consecutive bf16 columns (= 4 swizzle chunks starting at chunk `ci0`) of row `row` into an A-operand slot
@@ -305,78 +330,98 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 if (etid < 128) reinterpret_cast<float4*>(s_sh2)[etid] = __ldg(reinterpret_cast<const float4*>(a.sh2[b]) + etid);
                 epi_sync();
                 const float* base_b = staged ? s_base + (obj - obj0) * 768 : base_obj + b * 768;
+                // Every epilogue loop below is software-pipelined over two register buffers: the tcgen05.ld of chunk c+1 is in
+                // flight while chunk c is converted (tcgen05.wait::ld waits for ALL outstanding loads, so the next load is
+                // issued right after the wait).
                 // ---- E1: skip branch R = bf16(lrelu(fc3 + base)), packed in place into TMEM ----
+                // half 0 packs columns [0,256) upwards into [0,128); half 1 packs [256,512) DOWNWARDS into [384,512): a warp
+                // only ever overwrites columns it has already read, and [128,384) is left free as one 256-column block
                 wait_mma();
-#pragma unroll 2
-                for (int cc = 0; cc < 8; ++cc) {
-                    // half 0 packs columns [0,256) upwards into [0,128); half 1 packs [256,512) DOWNWARDS into [384,512): a
-                    // warp only ever overwrites columns it has already read, and [128,384) is left free as one 256-column block
-                    const int c = half ? 7 - cc : cc;
-                    uint32_t r[32];
-                    tmem_ld_32x32(tlane + half * 256 + c * 32, r);
-                    const float* bp = base_b + 256 + half * 256 + c * 32;
-                    float4 bv[8];
+                {
+                    uint32_t ra[32], rb[32];
+                    auto col_of = [&](int cc) { return half ? 7 - cc : cc; };
+                    auto e1 = [&](int c, const uint32_t (&r)[32]) {
+                        const float* bp = base_b + 256 + half * 256 + c * 32;
+                        uint32_t o[16];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) bv[j] = *reinterpret_cast<const float4*>(bp + 4 * j);
-                    tmem_ld_wait();
-                    uint32_t o[16];
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bv = *reinterpret_cast<const float4*>(bp + 4 * j);
+                            o[2 * j] = lrelu_pack2(r[4 * j], r[4 * j + 1], bv.x, bv.y);
+                            o[2 * j + 1] = lrelu_pack2(r[4 * j + 2], r[4 * j + 3], bv.z, bv.w);
+                        }
+                        tmem_st_32x16(tlane + (half ? 384 : 0) + c * 16, o);
+                    };
+                    tmem_ld_32x32(tlane + half * 256 + col_of(0) * 32, ra);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float x0 = __uint_as_float(r[4 * j]) + bv[j].x, x1 = __uint_as_float(r[4 * j + 1]) + bv[j].y;
-                        const float x2 = __uint_as_float(r[4 * j + 2]) + bv[j].z, x3 = __uint_as_float(r[4 * j + 3]) + bv[j].w;
-                        o[2 * j] = pack_bf16x2(fmaxf(x0, 0.2f * x0), fmaxf(x1, 0.2f * x1));
-                        o[2 * j + 1] = pack_bf16x2(fmaxf(x2, 0.2f * x2), fmaxf(x3, 0.2f * x3));
+                    for (int cc = 0; cc < 8; cc += 2) {
+                        tmem_ld_wait();
+                        tmem_ld_32x32(tlane + half * 256 + col_of(cc + 1) * 32, rb);
+                        e1(col_of(cc), ra);
+                        tmem_ld_wait();
+                        if (cc + 2 < 8) tmem_ld_32x32(tlane + half * 256 + col_of(cc + 2) * 32, ra);
+                        e1(col_of(cc + 1), rb);
                     }
-                    tmem_st_32x16(tlane + (half ? 384 : 0) + c * 16, o);
                 }
                 tmem_st_wait();
                 arrive_epi();
                 // ---- E2: H = bf16(lrelu(fc1 + base)) -> slots 0..3 (bn1 is folded into the weights and the base) ----
                 wait_mma();
-#pragma unroll 2
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(tlane + 128 + half * 128 + c * 32, r);
-                    const int n0 = half * 128 + c * 32;
-                    float4 bv[8];
+                {
+                    uint32_t ra[32], rb[32];
+                    auto e2 = [&](int c, const uint32_t (&r)[32]) {
+                        const float* bp = base_b + half * 128 + c * 32;
+                        uint32_t o[16];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) bv[j] = *reinterpret_cast<const float4*>(base_b + n0 + 4 * j);
-                    tmem_ld_wait();
-                    float v[32];
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 bv = *reinterpret_cast<const float4*>(bp + 4 * j);
+                            o[2 * j] = lrelu_pack2(r[4 * j], r[4 * j + 1], bv.x, bv.y);
+                            o[2 * j + 1] = lrelu_pack2(r[4 * j + 2], r[4 * j + 3], bv.z, bv.w);
+                        }
+                        store_row32p(sA + (half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, o);
+                    };
+                    const uint32_t t0 = tlane + 128 + half * 128;
+                    tmem_ld_32x32(t0, ra);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const float x0 = __uint_as_float(r[4 * j]) + bv[j].x, x1 = __uint_as_float(r[4 * j + 1]) + bv[j].y;
-                        const float x2 = __uint_as_float(r[4 * j + 2]) + bv[j].z, x3 = __uint_as_float(r[4 * j + 3]) + bv[j].w;
-                        v[4 * j] = fmaxf(x0, 0.2f * x0); v[4 * j + 1] = fmaxf(x1, 0.2f * x1);
-                        v[4 * j + 2] = fmaxf(x2, 0.2f * x2); v[4 * j + 3] = fmaxf(x3, 0.2f * x3);
+                    for (int c = 0; c < 4; c += 2) {
+                        tmem_ld_wait();
+                        tmem_ld_32x32(t0 + (c + 1) * 32, rb);
+                        e2(c, ra);
+                        tmem_ld_wait();
+                        if (c + 2 < 4) tmem_ld_32x32(t0 + (c + 2) * 32, ra);
+                        e2(c + 1, rb);
                     }
-                    store_row32(sA + (half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
                 }
                 arrive_epi();
                 // ---- E3 / E4: Xout = bf16(lrelu(R + fc2 + sh2)) -> slots 4..7 (h = 0) / 0..3 (h = 1) ----
                 for (int h = 0; h < 2; ++h) {
                     wait_mma();
-#pragma unroll 2
-                    for (int c = 0; c < 4; ++c) {
-                        uint32_t r[32], rr[16];
-                        tmem_ld_32x32(tlane + 128 + half * 128 + c * 32, r);
-                        tmem_ld_32x16(tlane + (h ? 384 : 0) + half * 64 + c * 16, rr);
-                        const int n0 = h * 256 + half * 128 + c * 32;
-                        float4 hv[8];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) hv[j] = *reinterpret_cast<const float4*>(s_sh2 + n0 + 4 * j);
-                        tmem_ld_wait();
-                        float v[32];
+                    uint32_t ra[32], rb[32], qa[16], qb[16];
+                    auto e3 = [&](int c, const uint32_t (&r)[32], const uint32_t (&rr)[16]) {
+                        const float* hp = s_sh2 + h * 256 + half * 128 + c * 32;
+                        uint32_t o[16];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
-                            const float x0 = __uint_as_float(r[4 * j]) + hv[j].x + bf16_lo(rr[2 * j]);
-                            const float x1 = __uint_as_float(r[4 * j + 1]) + hv[j].y + bf16_hi(rr[2 * j]);
-                            const float x2 = __uint_as_float(r[4 * j + 2]) + hv[j].z + bf16_lo(rr[2 * j + 1]);
-                            const float x3 = __uint_as_float(r[4 * j + 3]) + hv[j].w + bf16_hi(rr[2 * j + 1]);
-                            v[4 * j] = fmaxf(x0, 0.2f * x0); v[4 * j + 1] = fmaxf(x1, 0.2f * x1);
-                            v[4 * j + 2] = fmaxf(x2, 0.2f * x2); v[4 * j + 3] = fmaxf(x3, 0.2f * x3);
+                            const float4 hv = *reinterpret_cast<const float4*>(hp + 4 * j);
+                            o[2 * j] = lrelu_pack3(r[4 * j], r[4 * j + 1], hv.x, hv.y, rr[2 * j]);
+                            o[2 * j + 1] = lrelu_pack3(r[4 * j + 2], r[4 * j + 3], hv.z, hv.w, rr[2 * j + 1]);
                         }
-                        store_row32(sA + ((h ? 0 : 4) + half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, v);
+                        store_row32p(sA + ((h ? 0 : 4) + half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, o);
+                    };
+                    const uint32_t t0 = tlane + 128 + half * 128, q0 = tlane + (h ? 384 : 0) + half * 64;
+                    tmem_ld_32x32(t0, ra);
+                    tmem_ld_32x16(q0, qa);
+#pragma unroll
+                    for (int c = 0; c < 4; c += 2) {
+                        tmem_ld_wait();
+                        tmem_ld_32x32(t0 + (c + 1) * 32, rb);
+                        tmem_ld_32x16(q0 + (c + 1) * 16, qb);
+                        e3(c, ra, qa);
+                        tmem_ld_wait();
+                        if (c + 2 < 4) {
+                            tmem_ld_32x32(t0 + (c + 2) * 32, ra);
+                            tmem_ld_32x16(q0 + (c + 2) * 16, qa);
+                        }
+                        e3(c + 1, rb, qb);
                     }
                     arrive_epi();
                 }
