@@ -43,6 +43,9 @@ def parse():
     ap.add_argument("--clouds", type=int, default=N_CLOUDS)
     ap.add_argument("--samples", type=int, default=N_SAMPLES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c3", choices=["c3", "train"],
+                    help="c3 = the headline inference metric; train = secondary C5 line (GAN + evaluator training step, global batch 4096)")
+    ap.add_argument("--batch", type=int, default=4096, help="global training batch (C5)")
     return ap.parse_args()
 
 
@@ -152,6 +155,87 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# --------------------------------------------------------------------------------------------- C5: training step (secondary)
+TRAIN_CFG = dict(latentD=5, n_hand_joints=12, is_train=True, model="dexgangrasp", is_wgan=False, bce_weight=1.0,
+                 train_ffhgenerator=True, train_ffhevaluator=True, beta1=0.9, weight_decay=5e-4, lr=1e-4, lr_gen=1e-4, lr_dis=1e-4,
+                 lr_policy="plateau", threshold_lr_policy_plateau=0.01, patience_lr_policy_plateau=5, weight_init_type="xavier",
+                 init_gain=0.02)
+
+
+def run_train(args, rank, world, local):
+    """C5 (BASELINE.json configs[4]): one step = DexGanGrasp.update_dexgangrasp (D step + G step) + update_dexevaluator on a
+    global batch of 4096 synthetic rows, sharded 4096/N per rank, gradients and BatchNorm statistics allreduced over NCCL
+    (train.py:233-260 drives the same two calls per batch).  Strong scaling: the global batch is fixed."""
+    import torch.distributed as dist
+    from dex_gan_grasp_b200 import _native, dataparallel, synth
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L = _native.lib()
+    _native.check(L.dexgg_device_check())
+    dev = torch.device("cuda", local)
+    model = DexGanGrasp(dict(TRAIN_CFG, gpu_ids=[local], precision=args.precision))
+    model.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    model.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    full = synth.synth_train_batch(args.batch, seed=11)
+    mine = {k: v.to(dev) for k, v in dataparallel.shard(full, rank, world).items()}
+    host = {k: v.pin_memory() for k, v in dataparallel.shard(full, rank, world).items()}
+
+    def step(src):
+        b = {k: v.clone() if src is mine else v.to(dev, non_blocking=True) for k, v in src.items()}
+        l1 = model.update_dexgangrasp(b, is_train_gen=True)
+        l2 = model.update_dexevaluator(b)
+        return l1, l2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step(mine)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    n0 = L.dexgg_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step(mine)
+    e1.record()
+    barrier()
+    launches = (L.dexgg_launch_count() - n0) // max(args.steps, 1)
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        l1, l2 = step(host)
+        loss_host = float(l1["total_loss_gen"]) + float(l2["total_loss_eva"])  # device -> host read of the step's result
+    torch.cuda.synchronize()
+    ms_e2e = 1e3 * (time.perf_counter() - t0) / args.steps
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    h2d = sum(v.numel() * v.element_size() for v in host.values())
+    if rank == 0:
+        line = {"metric": "samples/sec (DexGenerator + Discriminator + DexEvaluator training step)", "value": args.batch / (float(t[0]) * 1e-3),
+                "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(t[0]),
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "f32 CUDA-core GEMMs" if args.precision == "fp32" else "bf16 tensor-core GEMMs / f32 accumulate, f32 master weights",
+                "data": "synthetic",
+                "config": {"workload": "C5 GAN + evaluator training step", "global_batch": args.batch, "rows_per_gpu": args.batch // world,
+                           "precision": args.precision, "optimizer": "Adam lr 1e-4 wd 5e-4 (fused multi-tensor kernel)",
+                           "l2": "working set (activations + weights + Adam state, > 500 MB) exceeds L2"},
+                "e2e": {"value": args.batch / (float(t[1]) * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d * world,
+                        "d2h_bytes_per_step": 8, "ms_per_step": float(t[1])},
+                "gpu_launches": int(launches), "clocks": clocks, "last_loss": loss_host}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 # --------------------------------------------------------------------------------------------- our arm
 def main():
     args = parse()
@@ -160,6 +244,13 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank)
+        return
+    if args.workload == "train":
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+        if "DEXGG_PRECISION" not in os.environ and "--precision" not in sys.argv:
+            args.precision = "fp32"
+        run_train(args, rank, world, local)
         return
     import torch.distributed as dist
     from dex_gan_grasp_b200 import _native, synth

@@ -1,0 +1,63 @@
+"""Data-parallel training step on real GPUs vs the single-GPU step on the concatenated batch.
+
+  torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/train_dp_check.py
+
+Every rank first runs the full-batch step alone (no process group), then the ranks run the sharded step with the NCCL
+gradient / BatchNorm-statistics exchange; losses, updated weights and BatchNorm running statistics must agree."""
+import copy, json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+from dex_gan_grasp_b200 import dataparallel, synth
+from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+import bench
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+B = int(os.environ.get("DP_BATCH", "512"))
+prec = os.environ.get("DEXGG_PRECISION", "fp32")
+
+
+def fresh():
+    m = DexGanGrasp(dict(bench.TRAIN_CFG, gpu_ids=[local], precision=prec))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(7))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(7))
+    return m
+
+
+full = synth.synth_train_batch(B, seed=11)
+z = synth.synth_latents(B, 5, seed=3)
+ref = fresh()
+lg = ref.update_dexgangrasp({k: v.to(dev) for k, v in full.items()}, is_train_gen=True, Zgen=z.to(dev))
+torch.cuda.synchronize()
+
+dist.init_process_group("nccl", device_id=dev)
+dp = fresh()
+n = B // world
+lg2 = dp.update_dexgangrasp({k: v.to(dev) for k, v in dataparallel.shard(full, rank, world).items()}, is_train_gen=True,
+                            Zgen=z[rank * n:(rank + 1) * n].to(dev))
+torch.cuda.synchronize()
+out = {"world": world, "batch": B, "precision": prec, "loss_abs_diff": {}, "max_weight_diff": 0.0, "max_buffer_diff": 0.0}
+for k in lg:
+    # per-rank losses are means over the local shard: average them over ranks to compare with the full-batch mean
+    t = torch.tensor([float(lg2[k])], device=dev, dtype=torch.float64)
+    dist.all_reduce(t)
+    out["loss_abs_diff"][k] = abs(float(t) / world - float(lg[k]))
+params = {k for k, _ in ref.DexGANGrasp.named_parameters()}
+sd_a, sd_b = ref.DexGANGrasp.state_dict(), dp.DexGANGrasp.state_dict()
+for k in sd_a:
+    if not sd_a[k].is_floating_point():
+        continue
+    d = float((sd_a[k].double() - sd_b[k].double()).abs().max())
+    key = "max_weight_diff" if k in params else "max_buffer_diff"
+    out[key] = max(out[key], d)
+# weights must be identical on every rank after the step
+flat = torch.cat([p.detach().reshape(-1) for p in dp.DexGANGrasp.parameters()])
+mx, mn = flat.clone(), flat.clone()
+dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+out["max_rank_divergence"] = float((mx - mn).abs().max())
+if rank == 0:
+    print(json.dumps(out), flush=True)
+dist.destroy_process_group()
