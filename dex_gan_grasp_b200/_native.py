@@ -51,6 +51,9 @@ SIGNATURES = {
     "dexgg_bn_backward_apply": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                         c_float, c_int64, c_int, c_void_p, c_int64, c_void_p]),
     "dexgg_adam_step": (c_int, [c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_int, c_void_p]),
+    "dexgg_magd_workspace_bytes": (c_size_t, [c_int]),
+    "dexgg_magd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                           c_void_p, c_void_p, c_size_t, c_void_p]),
     "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
 }
 

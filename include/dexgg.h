@@ -184,6 +184,20 @@ int dexgg_bn_backward_apply(const float* g, int64_t ldg, const float* x, int64_t
 int dexgg_adam_step(const void* chunks_dev, int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay,
                     int step, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Mean Absolute Grasp Deviation between a predicted grasp set and a ground-truth set.
+ * Replaces magd_for_grasp_distribution (eval.py:101-137) and its pairwise helpers (eval.py:48-99): every predicted
+ * grasp is matched to the ground-truth grasp with the smallest SQUARED translation distance (first index on ties);
+ *   sums_out[0] = sum of those squared translation distances     sums_out[1] = sum of geodesic rotation angles (rad)
+ *   sums_out[2] = sum of squared joint-configuration distances   sums_out[3] = coverage = distinct matches / M
+ * pred_* [N,3] [N,9] [N,n_joints], gt_* [M,3] [M,9] [M,n_joints], all f32 row-major on the device; match_out [N] i32 and
+ * per_grasp_out [N,3] f32 (transl, rot, joint terms) may be NULL; sums_out 4 doubles on the device.
+ * ---------------------------------------------------------------------------------------------------------- */
+size_t dexgg_magd_workspace_bytes(int M);
+int dexgg_magd(const float* pred_transl, const float* pred_rot, const float* pred_joint, int64_t N, const float* gt_transl,
+               const float* gt_rot, const float* gt_joint, int M, int n_joints, int32_t* match_out, float* per_grasp_out,
+               double* sums_out, void* workspace, size_t workspace_bytes, void* stream);
+
 /* FP32-pipe micro-benchmark used for the BPS roofline denominator: runs `iters` rounds of 8
  * independent FFMA (kind 0), FFMA2 (kind 1), FADD2 (kind 2) or FMNMX3 (kind 3) chains per thread on a full grid and
  * returns the elapsed milliseconds in *ms and the number of lane-operations executed in *lane_ops. */
