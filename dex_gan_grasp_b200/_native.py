@@ -38,6 +38,7 @@ SIGNATURES = {
     "dexgg_linear_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
     "dexgg_f32_to_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
+    "dexgg_f32_to_bf16_t": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_rot6d_forward": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
     "dexgg_rot6d_backward": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "dexgg_col_sum": (c_int, [c_void_p, c_int64, c_int64, c_int, c_void_p, c_void_p]),

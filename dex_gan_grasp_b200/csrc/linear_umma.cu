@@ -263,7 +263,8 @@ int make_tmap_bf16(CUtensorMap* out, const void* base, int64_t rows, int64_t col
 
 int linear_bf16(const LinearB16& q, cudaStream_t st) {
     DEXGG_REQUIRE(q.M >= 0 && q.N >= 1 && q.K >= 1 && q.A && q.W && (q.C16 || q.C32), "linear_bf16: bad arguments (M=%d N=%d K=%d)", q.M, q.N, q.K);
-    DEXGG_REQUIRE(q.K % 8 == 0, "linear_bf16: K must be a multiple of 8 (got %d)", q.K);
+    // K itself may be any length: the tensor maps clip at K and the TMA zero-fills the rest of the last k-block; only the
+    // row pitches must be 16-byte multiples (checked by make_tmap_bf16)
     if (q.M == 0) return DEXGG_OK;
     int BN = 256;
     if (q.N <= 32) BN = 32;
@@ -298,9 +299,41 @@ __global__ void f32_to_bf16_kernel(const float* __restrict__ src, int64_t lds, _
     dst[r * ldd + c] = __float2bfloat16_rn(src[r * lds + c]);
 }
 
+// dst[c, r] = bf16(src[r, c]): the K-major operand of a GEMM that contracts over the ROWS of src (wgrad: dY^T, X^T; dgrad: W^T)
+__global__ void f32_to_bf16_t_kernel(const float* __restrict__ src, int64_t lds, __nv_bfloat16* __restrict__ dst, int64_t ldd,
+                                     int64_t rows, int cols) {
+    __shared__ float tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.y * 32;
+    const int c0 = blockIdx.x * 32;
+    for (int i = threadIdx.y; i < 32; i += 8) {
+        const int64_t r = r0 + i;
+        const int c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < rows && c < cols) ? src[r * lds + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += 8) {
+        const int c = c0 + i;
+        const int64_t r = r0 + threadIdx.x;
+        if (c < cols && r < rows) dst[(int64_t)c * ldd + r] = __float2bfloat16_rn(tile[threadIdx.x][i]);
+    }
+}
+
 }  // namespace dexgg
 
 using namespace dexgg;
+
+extern "C" int dexgg_f32_to_bf16_t(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(rows >= 0 && cols >= 1 && (rows == 0 || (src && dst)) && ldd >= rows, "f32_to_bf16_t: bad arguments");
+    if (rows == 0) return DEXGG_OK;
+    const dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
+    DEXGG_REQUIRE(grid.y <= 65535, "f32_to_bf16_t: too many rows (%lld)", (long long)rows);
+    f32_to_bf16_t_kernel<<<grid, dim3(32, 8), 0, static_cast<cudaStream_t>(stream)>>>(src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, rows,
+                                                                                     cols);
+    ::dexgg::count_launches(1);
+    DEXGG_LAUNCH_OK("f32_to_bf16_t_kernel");
+    return DEXGG_OK;
+}
 
 // C ABI: one bf16 tensor-core layer on caller-provided bf16 operands (isolated test / building block).
 extern "C" int dexgg_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, const float* bias,

@@ -320,7 +320,14 @@ class DexGanGrasp(object):
             self.scheduler_dexgenerator.step(eval_loss_dict['total_loss_gen'])
 
     # ------------------------------------------------------------------ training steps (:739-823)
+    def _train_precision(self):
+        """cfg['precision'] selects the GEMM arithmetic of the training step too: 'fp32' (default, 1e-4 parity with the
+        reference) or 'bf16' (tcgen05 tensor cores, fp32 accumulation and fp32 master weights)."""
+        from . import train_ops
+        train_ops.set_precision(self.cfg.get("precision", "fp32"))
+
     def update_dexevaluator(self, data):
+        self._train_precision()
         self.DexEvaluator.train()
         out = self.DexEvaluator(data)
         total_loss_dexevaluator, loss_dict_dexevaluator = self.compute_loss_dexevaluator(out)
@@ -339,6 +346,7 @@ class DexGanGrasp(object):
         """dexgangrasp.py:757-823 (non-WGAN branch).  `Zgen` (optional) lets a test supply the latent batch."""
         if self.is_wgan:
             raise NotImplementedError("WGAN-GP variant: SURVEY.md §8f 'next'")
+        self._train_precision()
         self.DexGANGrasp.train()
         G, D = self.DexGANGrasp.generator, self.DexGANGrasp.discriminator
         n_samples = real_data["bps_object"].shape[0]

@@ -57,8 +57,53 @@ def _ld(x):
     return x.stride(0) if x.shape[0] > 1 else x.shape[1]
 
 
+_PRECISION = "fp32"
+
+
+def set_precision(p):
+    """'fp32' (CUDA-core GEMMs, the 1e-4 parity mode) or 'bf16' (tcgen05 GEMMs: bf16 operands, fp32 accumulation in TMEM, fp32
+    master weights / gradients / BatchNorm / Adam - BASELINE.json configs[4]).  Set by DexGanGrasp from cfg['precision']."""
+    global _PRECISION
+    if p not in ("fp32", "bf16"):
+        raise ValueError(f"precision must be 'fp32' or 'bf16', got {p!r}")
+    _PRECISION = p
+
+
+def _up8(n):
+    return (n + 7) // 8 * 8
+
+
+def _to_bf16(x, transpose, R, C):
+    """bf16 copy of the leading [R, C] part of a row-major fp32 matrix (or of its transpose), row pitch padded to 8
+    elements (16 bytes, TMA)."""
+    dev = x.device
+    with torch.cuda.device(dev):
+        if transpose:
+            out = torch.empty((C, _up8(R)), dtype=torch.bfloat16, device=dev)
+            _native.check(_L().dexgg_f32_to_bf16_t(x.data_ptr(), _ld(x), out.data_ptr(), out.shape[1], R, C, _st(dev)))
+        else:
+            out = torch.empty((R, _up8(C)), dtype=torch.bfloat16, device=dev)
+            _native.check(_L().dexgg_f32_to_bf16(x.data_ptr(), _ld(x), out.data_ptr(), out.shape[1], R, C, _st(dev)))
+    return out
+
+
+def _raw_linear_bf16(A, trans_a, W, trans_w, M, N, K, bias, act):
+    """Same contract as raw_linear on the tensor cores: both operands are brought to K-major bf16 (a transposing convert
+    where the fp32 operand is stored with the contraction index as its row index), fp32 result."""
+    dev = A.device
+    a16 = _to_bf16(A, True, K, M) if trans_a else _to_bf16(A, False, M, K)   # [M, K]
+    w16 = _to_bf16(W, True, K, N) if trans_w else _to_bf16(W, False, N, K)   # [N, K]
+    out = torch.empty((M, N), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _native.check(_L().dexgg_linear_bf16(a16.data_ptr(), a16.shape[1], w16.data_ptr(), w16.shape[1], M, N, K, _native.ptr(bias),
+                                             None, None, None, 0, int(act), None, out.data_ptr(), N, _st(dev)))
+    return out
+
+
 def raw_linear(A, trans_a, W, trans_w, M, N, K, bias=None, act=0, accumulate=0, out=None):
-    """C[M,N] = act(op(A) . op(W)^T + bias) through dexgg_linear_f32."""
+    """C[M,N] = act(op(A) . op(W)^T + bias) through dexgg_linear_f32 (or the tcgen05 kernel in bf16 mode)."""
+    if _PRECISION == "bf16" and not accumulate and out is None and M >= 1:
+        return _raw_linear_bf16(A, trans_a, W, trans_w, M, N, K, bias, act)
     dev = A.device
     if out is None:
         out = torch.empty((M, N), dtype=torch.float32, device=dev)

@@ -144,12 +144,15 @@ int dexgg_linear_f32(const float* A, int64_t lda, int trans_a, const float* W, i
 
 /* One fused linear layer on the 5th-generation tensor cores (tcgen05, bf16 operands, fp32 accumulation in TMEM):
  * C = act(scale * (A·Wᵀ + bias) + shift + residual).  A [M,K] and W [N,K] are bf16, row-major, row pitch a multiple of
- * 16 bytes; K a multiple of 8.  Output bf16 (C_bf16) and / or fp32 (C_f32), row pitch ldc elements.
- * dexgg_f32_to_bf16 converts a strided fp32 matrix to bf16 (round to nearest even). */
+ * 16 bytes; K any length.  Output bf16 (C_bf16) and / or fp32 (C_f32), row pitch ldc elements.
+ * dexgg_f32_to_bf16 converts a strided fp32 matrix to bf16 (round to nearest even); dexgg_f32_to_bf16_t writes the
+ * TRANSPOSE (dst[c*ldd + r] = src[r*lds + c], ldd >= rows) - the K-major operand of a product that contracts over the rows
+ * of src, as the training step's wgrad (dW = dY^T X) and dgrad (dX = dY W) need (models/dexgangrasp.py:739-823). */
 int dexgg_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, const float* bias,
                       const float* scale, const float* shift, const void* residual_bf16, int64_t ldr, int act, void* C_bf16,
                       float* C_f32, int64_t ldc, void* stream);
 int dexgg_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream);
+int dexgg_f32_to_bf16_t(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream);
 
 /* rot6d -> rotation matrix (utils.rot_matrix_from_ortho6d, DexGanGrasp/utils/utils.py:380-394) and its backward
  * (used by the generator training step, dexgangrasp.py:776 and losses.py:67).  r6 [M,6], rot / g_rot [M,9], g_r6 [M,6]. */

@@ -166,3 +166,81 @@ def test_eval_losses_after_training(model):
     assert np.isfinite(float(e["total_loss_eva"]))
     pos, neg, pred, gt = model.eval_dexevaluator_accuracy(copy.deepcopy(batch))
     assert pred.shape == gt.shape
+
+
+# ------------------------------------------------------------------ bf16 tensor-core training mode (BASELINE.json configs[4])
+BF16_LOSS_TOL = 2e-2   # relative; bf16 operand rounding (2^-9) through ~10 GEMMs, fp32 accumulation
+BF16_GRAD_TOL = 1e-1   # relative L2 norm of a gradient tensor against the fp32 oracle (worst seen: 6.1e-2, a BatchNorm gamma)
+
+
+@pytest.fixture()
+def model_bf16():
+    from dex_gan_grasp_b200 import train_ops
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    m = DexGanGrasp(dict(CFG, precision="bf16"))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    yield m
+    train_ops.set_precision("fp32")
+
+
+def _grad_rel(got, ref):
+    ref = ref.double()
+    return float((got.detach().cpu().double() - ref).norm()) / max(float(ref.norm()), 1e-30)
+
+
+def test_bf16_gan_step_close_to_oracle(model_bf16):
+    """Same step as test_gan_step_matches_oracle with every GEMM (forward, dgrad, wgrad) on the tcgen05 kernel: losses within
+    2e-2 relative, gradients within 1e-1 in the relative L2 norm, weights move by at most Adam's lr per step, BatchNorm
+    running statistics (computed in fp32 from bf16-GEMM outputs) within 1e-2."""
+    batch = _batch()
+    z = synth.synth_latents(B, 5, seed=3)
+    sd = {k: v.clone() for k, v in synth.synth_gan_state_dict(SEED).items()}
+    ref_losses, ref_grads = no.gan_step(sd, {}, {}, copy.deepcopy(batch), z.clone(), is_train_gen=True)
+    ours = model_bf16.update_dexgangrasp(copy.deepcopy(batch), is_train_gen=True, Zgen=z.cuda())
+    torch.cuda.synchronize()
+    for k, v in ref_losses.items():
+        assert abs(float(ours[k]) - v) < BF16_LOSS_TOL * max(1.0, abs(v)), (k, float(ours[k]), v)
+    named = dict(model_bf16.DexGANGrasp.named_parameters())
+    worst = 0.0
+    for k, g in ref_grads["g"].items():
+        if k.endswith(("fc1.bias", "fc2.bias")) or float(g.norm()) < 1e-6:
+            continue  # bias in front of a train-mode BatchNorm: true gradient zero
+        worst = max(worst, _grad_rel(named[k].grad, g))
+        assert _grad_rel(named[k].grad, g) < BF16_GRAD_TOL, (k, _grad_rel(named[k].grad, g))
+    w0 = synth.synth_gan_state_dict(SEED)
+    for k, p in named.items():
+        assert float((p.detach().cpu() - w0[k]).abs().max()) <= 1.05e-4, k  # |Adam step 1| <= lr
+    for k, v in model_bf16.DexGANGrasp.state_dict().items():
+        if "running_" in k:
+            assert md(v, sd[k]) < 1e-2 * max(1.0, float(sd[k].abs().max())), k
+
+
+def test_bf16_evaluator_step_close_to_oracle(model_bf16):
+    batch = _batch()
+    g = torch.Generator().manual_seed(5)
+    masks = [(torch.rand(B, 512, generator=g) >= 0.3).float() / 0.7 for _ in range(3)]
+    sd = {k: v.clone() for k, v in synth.synth_eva_state_dict(SEED).items()}
+    ref_losses, ref_grads = no.evaluator_step(sd, {}, copy.deepcopy(batch), dropout_masks=masks)
+    model_bf16.DexEvaluator.dropout_masks = [m.cuda() for m in masks]
+    ours = model_bf16.update_dexevaluator(copy.deepcopy(batch))
+    model_bf16.DexEvaluator.dropout_masks = None
+    for k, v in ref_losses.items():
+        assert abs(float(ours[k]) - v) < BF16_LOSS_TOL * max(1.0, abs(v)), (k, float(ours[k]), v)
+    named = dict(model_bf16.DexEvaluator.named_parameters())
+    for k, gr in ref_grads.items():
+        if k.endswith(("fc1.bias", "fc2.bias")) or float(gr.norm()) < 1e-6:
+            continue
+        assert _grad_rel(named[k].grad, gr) < BF16_GRAD_TOL, (k, _grad_rel(named[k].grad, gr))
+
+
+def test_bf16_training_reduces_the_loss(model_bf16):
+    """20 bf16 steps on one batch: the generator's reconstruction losses must go down (the optimisation works end to end)."""
+    batch = _batch()
+    first = last = None
+    for it in range(20):
+        out = model_bf16.update_dexgangrasp(copy.deepcopy(batch))
+        v = float(out["transl_loss"]) + float(out["conf_loss"])
+        first = v if first is None else first
+        last = v
+    assert np.isfinite(last) and last < first, (first, last)
