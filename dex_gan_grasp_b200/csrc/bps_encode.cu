@@ -219,6 +219,272 @@ bps_nn_packed_kernel(const float* __restrict__ basis, int P, const float* __rest
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Filtered search (default): the scan runs on the EXPANDED form  a(k) = |x_k|^2 - 2 b.x_k  (= d2 - |b|^2, three FFMA per pair
+// instead of the six FP32-pipe operations of the direct form) and only FILTERS; the reference arithmetic (direct differences,
+// search_d2) is then evaluated on the few candidates, so indices and distances stay bit-exact.
+//   * |a_fp32(k) - a_exact(k)| <= E = 8u (3C^2 + 2 |b|_1 C),  u = 2^-24, C = max |coordinate| of the CTA's point range
+//     (three fma roundings on intermediates bounded by 3C^2 + 2|b|_1 C, plus the three roundings of |x|^2);
+//   * the fp32 direct-form winner k* has exact d2 within (1 + 9u) of the exact minimum, so
+//     a_fp32(k*) <= min_k a_fp32(k) + 2E + 9u (|b|_2 + sqrt(3) C)^2 =: M  (the kernel uses 1.5 M, one value per thread: the
+//     maximum over its R basis points);
+//   * online rule per chunk with value v = min a over the chunk and running minimum m: v < m - M clears the
+//     candidate list (every earlier chunk is > final minimum + M), v <= m + M appends the chunk (chunks of BPSF_CHUNK points here).  The list keeps the last
+//     two chunks and a count in one register; a count above two (near-ties in more than two chunks: practically never)
+//     falls back to an exact scan of the whole range for that basis point;
+//   * masked points carry (0,0,0) with |x|^2 = +inf, so they never win and never produce a NaN.
+constexpr int BPSF_W_FLOATS = BPS_TILE + BPS_CHUNK;
+constexpr int BPSF_CHUNK = 32;   // points per candidate chunk of the filter
+constexpr int BPSF_SUBS = BPSF_CHUNK / 32;  // points per lane in the exact evaluation of a chunk
+
+__device__ __forceinline__ f32x2 filter_a2(f32x2 nbx, f32x2 nby, f32x2 nbz, float x, float y, float z, float w) {
+    return fma2(nbx, pack2(x, x), fma2(nby, pack2(y, y), fma2(nbz, pack2(z, z), pack2(w, w))));
+}
+
+template <int R>
+__global__ void __launch_bounds__(BPS_THREADS, 3)
+bps_nn_filter_kernel(const float* __restrict__ basis, int P, const float* __restrict__ pts,
+                     const int64_t* __restrict__ offsets, int64_t uniform_n, int64_t total_points, int nsplit,
+                     unsigned long long* __restrict__ keys) {
+    static_assert(R % 2 == 0, "R must be even");
+    extern __shared__ __align__(128) unsigned char bps_smem[];
+    float* stage0 = reinterpret_cast<float*>(bps_smem);
+    float* stage1 = stage0 + BPS_STAGE_FLOATS;
+    float* s_w = stage1 + BPS_STAGE_FLOATS;                              // [BPSF_W_FLOATS] |x|^2 of the current tile
+    uint32_t* s_pack = reinterpret_cast<uint32_t*>(s_w + BPSF_W_FLOATS);  // [R][BPS_THREADS] candidate lists
+    __shared__ uint64_t bar[2];
+    __shared__ uint32_t s_cmax;
+
+    const int tid = threadIdx.x;
+    const int b = blockIdx.y;
+    const int64_t o0 = offsets ? offsets[b] : (int64_t)b * uniform_n;
+    const int64_t o1 = offsets ? offsets[b + 1] : o0 + uniform_n;
+    const int64_t n = o1 - o0;
+    const int64_t len = (((n + nsplit - 1) / nsplit) + 3) & ~(int64_t)3;
+    const int64_t r0 = o0 + (int64_t)blockIdx.z * len;
+    const int64_t r1 = (r0 + len < o1) ? r0 + len : o1;
+    if (r0 >= r1) return;  // uniform for the CTA
+    const int64_t g0 = r0 & ~(int64_t)3;
+    const int64_t span = r1 - g0;
+    const int ntiles = (int)((span + BPS_TILE - 1) / BPS_TILE);
+    const int64_t bulk_end = total_points & ~(int64_t)3;
+
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        mbar_fence_init();
+        s_cmax = 0u;
+    }
+    __syncthreads();
+
+    auto issue = [&](int t) {  // tid 0 only
+        float* dst = (t & 1) ? stage1 : stage0;
+        const int64_t gs = g0 + (int64_t)t * BPS_TILE;
+        int64_t cnt = span - (int64_t)t * BPS_TILE;
+        if (cnt > BPS_TILE) cnt = BPS_TILE;
+        int64_t ge4 = gs + ((cnt + 3) & ~(int64_t)3);
+        if (ge4 > bulk_end) ge4 = bulk_end;
+        if (ge4 > gs) {
+            const uint32_t bytes = (uint32_t)((ge4 - gs) * 12);
+            fence_proxy_async();
+            mbar_expect_tx(&bar[t & 1], bytes);
+            bulk_g2s(dst, pts + 3 * gs, bytes, &bar[t & 1]);
+        } else {
+            mbar_arrive(&bar[t & 1]);
+        }
+    };
+    if (tid == 0) issue(0);
+
+    // ---- C = max |coordinate| over the range (the first tile's copy is in flight meanwhile) ----
+    {
+        float c = 0.f;
+        for (int64_t i = 3 * r0 + tid; i < 3 * r1; i += BPS_THREADS) c = fmaxf(c, fabsf(pts[i]));
+        for (int o = 16; o; o >>= 1) c = fmaxf(c, __shfl_xor_sync(0xffffffffu, c, o));
+        if ((tid & 31) == 0) atomicMax(&s_cmax, __float_as_uint(c));  // c >= 0 (or NaN / inf, which order above)
+    }
+
+    const int pbase = blockIdx.x * (BPS_THREADS * R) + tid;
+    f32x2 nbx[R / 2], nby[R / 2], nbz[R / 2];
+    float b1max = 0.f, b2max = 0.f;
+#pragma unroll
+    for (int j = 0; j < R / 2; ++j) {
+        float c[2][3];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int p = pbase + (2 * j + h) * BPS_THREADS;
+            const bool ok = p < P;
+            c[h][0] = ok ? basis[3 * p] : 0.f;
+            c[h][1] = ok ? basis[3 * p + 1] : 0.f;
+            c[h][2] = ok ? basis[3 * p + 2] : 0.f;
+            b1max = fmaxf(b1max, fabsf(c[h][0]) + fabsf(c[h][1]) + fabsf(c[h][2]));
+            b2max = fmaxf(b2max, sqrtf(c[h][0] * c[h][0] + c[h][1] * c[h][1] + c[h][2] * c[h][2]));
+        }
+        nbx[j] = pack2(-2.f * c[0][0], -2.f * c[1][0]);
+        nby[j] = pack2(-2.f * c[0][1], -2.f * c[1][1]);
+        nbz[j] = pack2(-2.f * c[0][2], -2.f * c[1][2]);
+    }
+    __syncthreads();
+    float margin;
+    {
+        const float C = __uint_as_float(s_cmax), u = 5.9604645e-8f;
+        const float E = 8.f * u * (3.f * C * C + 2.f * b1max * C);
+        const float dm = b2max + 1.7320508f * C;
+        margin = 1.5f * (2.f * E + 9.f * u * dm * dm);  // NaN / inf coordinates give a NaN / inf margin: every chunk then
+    }                                                    // overflows into the exact fallback scan
+    float best[R];
+    uint32_t pack[R];  // [31:18] last candidate chunk, [17:4] the one before, [3:0] count (saturating)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        best[r] = __int_as_float(0x7f800000);
+        pack[r] = 0u;
+    }
+
+    for (int t = 0; t < ntiles; ++t) {
+        if (tid == 0 && t + 1 < ntiles) issue(t + 1);
+        float* st = (t & 1) ? stage1 : stage0;
+        mbar_wait(&bar[t & 1], (t >> 1) & 1);
+        const int64_t gs = g0 + (int64_t)t * BPS_TILE;
+        int cnt = (int)((span - (int64_t)t * BPS_TILE) < BPS_TILE ? (span - (int64_t)t * BPS_TILE) : BPS_TILE);
+        const int npad = (cnt + BPS_CHUNK - 1) & ~(BPS_CHUNK - 1);
+        const int lo_valid = (t == 0) ? (int)(r0 - g0) : 0;
+        int bulk_local_end = (int)((bulk_end - gs) < 0 ? 0 : ((bulk_end - gs) > cnt ? cnt : (bulk_end - gs)));
+        // ---- fix-up + |x|^2: masked points become (0,0,0) with w = +inf; the <= 3 points past the last 48-byte group of the
+        // whole buffer are plain-loaded ----
+        for (int j = tid; j < npad; j += BPS_THREADS) {
+            float x = 0.f, y = 0.f, z = 0.f, w = __int_as_float(0x7f800000);
+            if (j >= lo_valid && j < cnt) {
+                if (j < bulk_local_end) {
+                    x = st[3 * j]; y = st[3 * j + 1]; z = st[3 * j + 2];
+                } else {
+                    const float* g = pts + 3 * (gs + j);
+                    x = g[0]; y = g[1]; z = g[2];
+                }
+                w = __fmaf_rn(z, z, __fmaf_rn(y, y, __fmul_rn(x, x)));
+            }
+            if (j < lo_valid || j >= bulk_local_end) {
+                st[3 * j] = x; st[3 * j + 1] = y; st[3 * j + 2] = z;
+            }
+            s_w[j] = w;
+        }
+        __syncthreads();
+
+        const float4* s4 = reinterpret_cast<const float4*>(st);
+        const float4* w4 = reinterpret_cast<const float4*>(s_w);
+        const int nquads = npad / 4;
+        const int nchunks = (npad + BPSF_CHUNK - 1) / BPSF_CHUNK;
+        for (int c = 0; c < nchunks; ++c) {
+            float cur[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) cur[r] = __int_as_float(0x7f800000);
+            const int q1 = min((c + 1) * (BPSF_CHUNK / 4), nquads);
+#pragma unroll 2
+            for (int q = c * (BPSF_CHUNK / 4); q < q1; ++q) {
+                const float4 v0 = s4[q * 3 + 0];
+                const float4 v1 = s4[q * 3 + 1];
+                const float4 v2 = s4[q * 3 + 2];
+                const float4 ww = w4[q];
+#pragma unroll
+                for (int j = 0; j < R / 2; ++j) {
+                    const f32x2 da = filter_a2(nbx[j], nby[j], nbz[j], v0.x, v0.y, v0.z, ww.x);
+                    const f32x2 db = filter_a2(nbx[j], nby[j], nbz[j], v0.w, v1.x, v1.y, ww.y);
+                    const f32x2 dc = filter_a2(nbx[j], nby[j], nbz[j], v1.z, v1.w, v2.x, ww.z);
+                    const f32x2 dd = filter_a2(nbx[j], nby[j], nbz[j], v2.y, v2.z, v2.w, ww.w);
+                    float a0, a1, b0, b1, c0, c1, d0, d1;
+                    unpack2(da, a0, a1);
+                    unpack2(db, b0, b1);
+                    unpack2(dc, c0, c1);
+                    unpack2(dd, d0, d1);
+                    cur[2 * j] = min3(min3(cur[2 * j], a0, b0), c0, d0);
+                    cur[2 * j + 1] = min3(min3(cur[2 * j + 1], a1, b1), c1, d1);
+                }
+            }
+            const uint32_t gc = (uint32_t)(t * (BPS_TILE / BPSF_CHUNK) + c);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {  // branch-free: selects only
+                const float v = cur[r], m = best[r];
+                const bool cand = (v < __int_as_float(0x7f800000)) && !(v > m + margin);  // a NaN margin keeps everything
+                const uint32_t pk = pack[r];
+                const uint32_t cn = (v < m - margin) ? 0u : (pk & 15u);  // a clear improvement drops the older candidates
+                const uint32_t npk = (gc << 18) | ((pk >> 14) & 0x3fff0u) | min(cn + 1u, 15u);
+                pack[r] = cand ? npk : pk;
+                best[r] = fminf(m, v);
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- exact arg-min on the candidates: one warp per basis point, reference arithmetic (search_d2), lowest index on ties.
+    // A lane evaluates its points of a chunk with all loads in flight together, and two basis points are
+    // handled per iteration, so the L2 latency of the candidate points is paid once per eight sub-chunks ----
+#pragma unroll
+    for (int r = 0; r < R; ++r) s_pack[r * BPS_THREADS + tid] = pack[r];
+    __syncthreads();
+    const int lane = tid & 31, warp = tid >> 5;
+    const int pblock = blockIdx.x * (BPS_THREADS * R);
+    const int total_chunks = (int)((span + BPSF_CHUNK - 1) / BPSF_CHUNK);
+    // per-lane best (distance bits, local point index) over chunk `ch`; strict < keeps the lower index on a tie
+    auto lane_chunk = [&](int ch, float qx, float qy, float qz, uint32_t& bd, uint32_t& bi) {
+        const int64_t gbase = g0 + (int64_t)ch * BPSF_CHUNK + lane;
+        float px[BPSF_SUBS], py[BPSF_SUBS], pz[BPSF_SUBS];
+#pragma unroll
+        for (int sub = 0; sub < BPSF_SUBS; ++sub) {
+            const int64_t g = gbase + sub * 32;
+            const bool ok = g >= r0 && g < r1;
+            const float* gp = pts + 3 * (ok ? g : r0);
+            px[sub] = gp[0]; py[sub] = gp[1]; pz[sub] = gp[2];
+        }
+#pragma unroll
+        for (int sub = 0; sub < BPSF_SUBS; ++sub) {
+            const int64_t g = gbase + sub * 32;
+            const float df = search_d2(qx, qy, qz, px[sub], py[sub], pz[sub]);
+            const uint32_t d = (g >= r0 && g < r1 && !(df != df)) ? __float_as_uint(df) : 0xffffffffu;  // d2 >= 0: bits order like values
+            if (d < bd) {
+                bd = d;
+                bi = (uint32_t)(g - g0);
+            }
+        }
+    };
+    auto commit = [&](int p, uint32_t bd, uint32_t bi) {  // warp reduction of the per-lane bests, then the atomic merge
+        const uint32_t mn = __reduce_min_sync(0xffffffffu, bd);
+        const uint32_t im = __reduce_min_sync(0xffffffffu, bd == mn ? bi : 0xffffffffu);
+        if (lane == 0 && mn != 0xffffffffu)
+            atomicMin(&keys[(size_t)b * P + p], make_key(__uint_as_float(mn), (uint32_t)(g0 + im - o0)));
+    };
+    auto one = [&](int e) {
+        const int p = pblock + e;
+        if (e >= BPS_THREADS * R || p >= P) return;
+        const uint32_t pk = s_pack[e];
+        const uint32_t cn = pk & 15u;
+        if (cn == 0u) return;  // no finite distance in this range
+        const float qx = basis[3 * p], qy = basis[3 * p + 1], qz = basis[3 * p + 2];
+        uint32_t bd = 0xffffffffu, bi = 0xffffffffu;
+        if (cn <= 2u) {
+            if (cn == 2u) lane_chunk((int)((pk >> 4) & 0x3fffu), qx, qy, qz, bd, bi);  // the earlier chunk first
+            lane_chunk((int)(pk >> 18), qx, qy, qz, bd, bi);
+        } else {
+            for (int ch = 0; ch < total_chunks; ++ch) lane_chunk(ch, qx, qy, qz, bd, bi);
+        }
+        commit(p, bd, bi);
+    };
+    for (int e = warp; e < BPS_THREADS * R; e += 2 * (BPS_THREADS / 32)) {
+        const int e1 = e + BPS_THREADS / 32;
+        const int p0 = pblock + e, p1 = pblock + e1;
+        const uint32_t pk0 = p0 < P ? s_pack[e] : 0u, pk1 = (e1 < BPS_THREADS * R && p1 < P) ? s_pack[e1] : 0u;
+        if ((pk0 & 15u) == 1u && (pk1 & 15u) == 1u) {  // common case: one candidate chunk each, eight loads in flight per lane
+            const float ax = basis[3 * p0], ay = basis[3 * p0 + 1], az = basis[3 * p0 + 2];
+            const float cx = basis[3 * p1], cy = basis[3 * p1 + 1], cz = basis[3 * p1 + 2];
+            uint32_t d0 = 0xffffffffu, i0 = 0xffffffffu, d1 = 0xffffffffu, i1 = 0xffffffffu;
+            lane_chunk((int)(pk0 >> 18), ax, ay, az, d0, i0);
+            lane_chunk((int)(pk1 >> 18), cx, cy, cz, d1, i1);
+            commit(p0, d0, i0);
+            commit(p1, d1, i1);
+        } else {
+            one(e);
+            one(e1);
+        }
+    }
+}
+
 // Simple scalar compare-select form: one thread per (cloud, basis point); cross-check of the packed kernel.
 __global__ void __launch_bounds__(128)
 bps_nn_scalar_kernel(const float* __restrict__ basis, int P, const float* __restrict__ pts,
@@ -322,6 +588,21 @@ static int launch_packed(const float* basis, int P, const float* pts, const int6
     return DEXGG_OK;
 }
 
+template <int R>
+static int launch_filter(const float* basis, int P, const float* pts, const int64_t* offsets, int B, int64_t uniform_n,
+                         int64_t total, int nsplit, unsigned long long* keys, cudaStream_t st) {
+    const size_t smem = (2 * BPS_STAGE_FLOATS + BPSF_W_FLOATS) * sizeof(float) + (size_t)R * BPS_THREADS * 4;
+    static bool attr_set = false;
+    if (!attr_set && smem > 48 * 1024) {
+        DEXGG_CUDA_OK(cudaFuncSetAttribute(bps_nn_filter_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    dim3 grid((P + BPS_THREADS * R - 1) / (BPS_THREADS * R), B, nsplit);
+    bps_nn_filter_kernel<R><<<grid, BPS_THREADS, smem, st>>>(basis, P, pts, offsets, uniform_n, total, nsplit, keys); ::dexgg::count_launches(1);
+    DEXGG_LAUNCH_OK("bps_nn_filter_kernel");
+    return DEXGG_OK;
+}
+
 extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
                                 int64_t max_cloud_points, int64_t total_points, float* dists, int32_t* idx, int flags,
                                 void* workspace, size_t workspace_bytes, void* stream) {
@@ -359,7 +640,10 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
                 if (s > 255) s = 255;
                 nsplit = (int)s;
             }
-            int rc = launch_packed<R>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st);
+            // the filtered kernel addresses chunks with 14 bits: at most 2^14 * 32 points per split
+            const bool direct = (flags & DEXGG_BPS_DIRECT) || (max_cloud_points + nsplit - 1) / nsplit + 8 > (int64_t)16384 * BPSF_CHUNK;
+            int rc = direct ? launch_packed<R>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st)
+                            : launch_filter<R>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st);
             if (rc != DEXGG_OK) return rc;
         }
     }

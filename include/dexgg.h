@@ -58,7 +58,9 @@ unsigned long long dexgg_launch_count(void);
  *   flags    DEXGG_BPS_* below.
  * ---------------------------------------------------------------------------------------------------------- */
 #define DEXGG_BPS_DEFAULT 0
-#define DEXGG_BPS_SCALAR 1     /* simple scalar compare-select kernel (cross-check of the packed kernel) */
+#define DEXGG_BPS_SCALAR 1     /* simple scalar compare-select kernel (cross-check of the packed kernels) */
+#define DEXGG_BPS_DIRECT 2     /* packed kernel that scans with the direct-difference form itself (6 FP32 ops / pair) instead of
+                                  the default expanded-form filter (3 FFMA / pair) + exact evaluation of the candidates */
 #define DEXGG_BPS_NSPLIT(n) (((n) & 0xff) << 8) /* force the number of point-range splits per cloud (0 = auto) */
 
 size_t dexgg_bps_workspace_bytes(int B, int P);

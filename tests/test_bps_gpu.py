@@ -10,6 +10,7 @@ pytestmark = pytest.mark.gpu
 
 NSPLIT = lambda n: (n & 0xff) << 8
 SCALAR = 1
+DIRECT = 2  # direct-difference scan instead of the default expanded-form filter + exact candidates
 
 
 def dev_encode(basis, clouds, flags=0):
@@ -24,7 +25,7 @@ def dev_encode(basis, clouds, flags=0):
     return d.cpu().numpy(), i.cpu().numpy()
 
 
-@pytest.mark.parametrize("flags", [0, SCALAR, NSPLIT(3)])
+@pytest.mark.parametrize("flags", [0, SCALAR, NSPLIT(3), DIRECT, DIRECT | NSPLIT(2)])
 def test_reference_fixtures_bit_exact(bps_golden, flags):
     basis = bps_golden["basis"]
     names = list(bps_golden["names"])
@@ -48,7 +49,7 @@ def test_encoder_class_surface(bps_golden):
     assert torch.allclose(r["deltas"].norm(dim=2), r["dists"], atol=1e-7)
 
 
-@pytest.mark.parametrize("flags", [0, NSPLIT(2), NSPLIT(5), SCALAR])
+@pytest.mark.parametrize("flags", [0, NSPLIT(2), NSPLIT(5), SCALAR, DIRECT, DIRECT | NSPLIT(5)])
 def test_ragged_random_vs_oracle(oracle_lib, bps_golden, flags):
     rng = np.random.default_rng(3)
     basis = bps_golden["basis"]
@@ -66,11 +67,35 @@ def test_ties_duplicates_lowest_index(oracle_lib):
     basis = rng.uniform(-0.2, 0.2, (300, 3)).astype(np.float32)  # P not a multiple of anything
     base = (rng.integers(-8, 8, (40, 3)) / 64.0).astype(np.float32)  # coarse grid -> many exact ties
     cloud = base[rng.integers(0, 40, 3000)]
-    for flags in (0, NSPLIT(4), SCALAR):
+    for flags in (0, NSPLIT(4), SCALAR, DIRECT):
         d, i = dev_encode(basis, [cloud, cloud[::-1].copy()], flags)
         for b, c in enumerate([cloud, cloud[::-1].copy()]):
             do, io = oracle_bps(oracle_lib, basis, c)
             assert np.array_equal(i[b], io) and np.array_equal(d[b], do)
+
+
+def test_filter_near_ties_and_off_centre_clouds(oracle_lib, bps_golden):
+    """Stress of the default kernel's filter (expanded form |x|^2 - 2 b.x, then exact evaluation of the candidates):
+    (a) thousands of points at almost the same distance from the basis points (a thin spherical shell around the basis
+    centroid, radial jitter at the 1e-7 level) - more than two chunks fall inside the error margin, which takes the exact
+    fallback scan; (b) clouds far from the origin (the margin grows with the coordinate magnitude); (c) a cloud holding the
+    basis points themselves (zero distances).  Indices and distances must stay bit-exact with the oracle."""
+    rng = np.random.default_rng(11)
+    basis = bps_golden["basis"][:512]
+    u = rng.normal(size=(6000, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    shell = (basis.mean(0) + 0.05 * u * (1.0 + 1e-7 * rng.normal(size=(6000, 1)))).astype(np.float32)
+    tiny = (basis[7] + 0.01 * u[:3000] * (1.0 + 3e-8 * rng.normal(size=(3000, 1)))).astype(np.float32)
+    far = (rng.normal(0, 0.05, (5000, 3)) + np.array([4.0, -7.0, 2.5])).astype(np.float32)
+    huge = (rng.normal(0, 30.0, (3000, 3))).astype(np.float32)
+    onb = np.concatenate([basis[::3], rng.normal(0, 0.1, (1000, 3)).astype(np.float32)])
+    clouds = [shell, tiny, far, huge, onb]
+    for flags in (0, NSPLIT(3)):
+        d, i = dev_encode(basis, clouds, flags)
+        for b, c in enumerate(clouds):
+            do, io = oracle_bps(oracle_lib, basis, c)
+            assert np.array_equal(i[b], io), (flags, b)
+            assert np.array_equal(d[b], do), (flags, b)
 
 
 def test_uniform_batch_and_large_cloud(oracle_lib, bps_golden):
@@ -96,6 +121,8 @@ def test_full_size_properties():
     d, i = bps_mod.bps_encode_device(basis, pts)
     d2, i2 = bps_mod.bps_encode_device(basis, pts, flags=SCALAR)
     assert torch.equal(d, d2) and torch.equal(i, i2)
+    d4, i4 = bps_mod.bps_encode_device(basis, pts, flags=DIRECT)
+    assert torch.equal(d, d4) and torch.equal(i, i4)
     perm = torch.randperm(2048, device="cuda", generator=g)
     d3, i3 = bps_mod.bps_encode_device(basis, pts[:, perm].contiguous())
     assert torch.equal(d, d3)  # no exact ties in continuous random data -> same winner, same distance
