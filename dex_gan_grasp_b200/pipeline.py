@@ -94,3 +94,60 @@ class GraspPipeline:
         h2d = clouds_host.numel() * 4 + z_host.numel() * 4
         d2h = host.numel() * 4 + cnt.numel() * 4
         return {"packed": host, "count": cnt}, h2d, d2h
+
+    def run_host_pipelined(self, steps, samples_per_object):
+        """Streaming form of run_host for a sequence of steps: `steps` is an iterable of (clouds_host, z_host) pinned CPU
+        tensors of one shape.  The inputs of step i+1 cross PCIe (H2D copy engine, own stream) while step i computes, and the
+        packed top-k result of step i returns on a third stream (D2H copy engine) while step i+1 computes; two device input
+        sets and two pinned result buffers rotate.  Yields ({"packed", "count"} CPU tensors, h2d bytes, d2h bytes) per step,
+        in order, each after its result has landed on the host."""
+        dev = self.device
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_h2d", None) is None:
+            self._h2d, self._d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        S = int(samples_per_object)
+        d_in, h_out = [None, None], [None, None]
+        done = [None, None]       # compute of the step that last used input set j has finished
+        pending = None            # (event, host tensors, byte counts) of the previous step
+        for i, (clouds_host, z_host) in enumerate(steps):
+            j = i & 1
+            if d_in[j] is None:
+                d_in[j] = (torch.empty(clouds_host.shape, dtype=torch.float32, device=dev),
+                           torch.empty(z_host.shape, dtype=torch.float32, device=dev))
+            d_clouds, d_z = d_in[j]
+            if done[j] is not None:
+                self._h2d.wait_event(done[j])
+            else:
+                self._h2d.wait_stream(main)
+            with torch.cuda.stream(self._h2d):
+                d_clouds.copy_(clouds_host, non_blocking=True)
+                d_z.copy_(z_host, non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(self._h2d)
+            main.wait_event(ready)
+            out = self.run_device(d_clouds, d_z, S)
+            B, k = out["idx"].shape
+            packed = torch.cat([out["score"].reshape(B, k, 1), out["idx"].float().reshape(B, k, 1), out["rot_matrix"].reshape(B, k, 9),
+                                out["transl"], out["joint_conf"]], dim=2)
+            cnt = out["count"]
+            done[j] = torch.cuda.Event()
+            done[j].record(main)
+            if h_out[j] is None:
+                h_out[j] = (torch.empty(packed.shape, dtype=torch.float32).pin_memory(), torch.empty(cnt.shape, dtype=torch.int32).pin_memory())
+            self._d2h.wait_event(done[j])
+            with torch.cuda.stream(self._d2h):
+                h_out[j][0].copy_(packed, non_blocking=True)
+                h_out[j][1].copy_(cnt, non_blocking=True)
+                landed = torch.cuda.Event()
+                landed.record(self._d2h)
+            packed.record_stream(self._d2h)
+            cnt.record_stream(self._d2h)
+            h2d = clouds_host.numel() * 4 + z_host.numel() * 4
+            d2h = packed.numel() * 4 + cnt.numel() * 4
+            if pending is not None:
+                pending[0].synchronize()
+                yield pending[1], pending[2], pending[3]
+            pending = (landed, {"packed": h_out[j][0], "count": h_out[j][1]}, h2d, d2h)
+        if pending is not None:
+            pending[0].synchronize()
+            yield pending[1], pending[2], pending[3]

@@ -297,3 +297,24 @@ def test_bf16_mode_many_objects_vs_fp32_mode(model, model_bf16, bps_golden):
     d16 = model_bf16.DexGANGrasp.discriminator.native_forward(bps, out32[0], out32[1], out32[2])
     print("bf16 vs fp32 mode: max |dp_eva| =", md(p16, p32), " max |dp_disc| =", md(d16, d32), " r6", md(out16[3], out32[3]))
     assert md(p16, p32) < BF16_SCORE_TOL and md(d16, d32) < BF16_SCORE_TOL
+
+
+def test_pipeline_streaming_equals_one_step_at_a_time(model):
+    """GraspPipeline.run_host_pipelined (copies of neighbouring steps overlap the compute, rotating buffers) returns, step by
+    step, exactly what run_host returns for the same inputs."""
+    from dex_gan_grasp_b200.pipeline import GraspPipeline
+    pipe = GraspPipeline(model.DexGANGrasp, model.DexEvaluator, k=5, thresh=0.5, z_offset=0.025)
+    B, S = 6, 200
+    steps = []
+    for i in range(5):
+        clouds = torch.from_numpy(synth.synth_clouds(B, 1024, seed0=50 + 10 * i)).pin_memory()
+        z = torch.randn((B * S, 5), generator=torch.Generator().manual_seed(i)).pin_memory()
+        steps.append((clouds, z))
+    want = [pipe.run_host(c, z, S)[0] for c, z in steps]
+    want = [{k: v.clone() for k, v in w.items()} for w in want]
+    n = 0
+    for (res, h2d, d2h), w in zip(pipe.run_host_pipelined(iter(steps), S), want):
+        assert torch.equal(res["count"], w["count"]) and torch.equal(res["packed"], w["packed"]), n
+        assert h2d == steps[0][0].numel() * 4 + steps[0][1].numel() * 4 and d2h > 0
+        n += 1
+    assert n == len(steps)
