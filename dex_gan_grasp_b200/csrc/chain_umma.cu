@@ -177,15 +177,24 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             const unsigned char* src = reinterpret_cast<const unsigned char*>(a.stream);
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
                 size_t off = 0;
-                for (int i = 0; i < n_main + CH_HEAD_TILES; ++i) {
-                    const uint32_t bytes = i < n_main ? (uint32_t)CH_SLOT_BYTES : HEAD_BYTES;
+                for (int i = 0; i < n_main; ++i) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     if (a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
-                    mbar_expect_tx(&full[stage], bytes);
-                    bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, bytes, &full[stage]); }
-                    off += bytes;
+                    mbar_expect_tx(&full[stage], CH_SLOT_BYTES);
+                    bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, CH_SLOT_BYTES, &full[stage]); }
+                    off += CH_SLOT_BYTES;
                     if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
                 }
+                // All eight head tiles in ONE copy (a copy costs ~140 cycles + bytes / 74 whatever its size), into a whole even /
+                // odd stage pair (n_main is even; the evaluator's 16 KB fill only the first stage).  (Issuing it one pair earlier,
+                // ahead of the last fc2 pair, was measured slower: it delays that pair and the head MMAs are not data-bound.)
+                for (int j = 0; j < 2; ++j) mbar_wait(&empty[stage + j], phase ^ 1);
+                if (a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
+                mbar_expect_tx(&full[stage], CH_HEAD_TILES * HEAD_BYTES);
+                bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, CH_HEAD_TILES * HEAD_BYTES, &full[stage]); }
+                mbar_arrive(&full[stage + 1]);  // the pair's second barrier completes its phase too (parities stay in step)
+                stage += 2;
+                if (stage == CH_STAGES) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -193,7 +202,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
         if (lane == 0) {
             const uint32_t idesc256 = umma_idesc_bf16(128, 256), idesc_h = umma_idesc_bf16(128, HEAD_ROWS);
             const uint32_t sA_u = smem_u32(sA), sR_u = smem_u32(sR);
-            int stage = 0, phase = 0, ephase = 0;
+            int stage = 0, phase = 0, ephase = 0, head_stage = 0, head_phase = 0;
             int dbg_n = 0;
             auto dbg = [&]() {
                 if (a.debug_clock && blockIdx.x == 0 && dbg_n < 256) a.debug_clock[dbg_n++] = clock64();
@@ -245,8 +254,21 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                         umma_commit(mma_bar); dbg();
                     }
                 }
-                wait_epi();  // heads over the 8 X slots
-                for (int s = 0; s < CH_HEAD_TILES; ++s) mma_tile(128, s, idesc_h, s == 0);
+                wait_epi();  // heads over the 8 X slots: the 8 weight tiles arrive as one copy in the next stage pair
+                head_stage = stage;
+                head_phase = phase;
+                stage += 2;
+                if (stage == CH_STAGES) { stage = 0; phase ^= 1; }
+                mbar_wait(&full[head_stage], head_phase);
+                tc_fence_after();
+                for (int s = 0; s < CH_HEAD_TILES; ++s) {
+                    const uint64_t ad = umma_desc_sw128_kmajor(sA_u + s * CH_SLOT_BYTES);
+                    const uint64_t bd = umma_desc_sw128_kmajor(sR_u + head_stage * CH_SLOT_BYTES + s * HEAD_BYTES);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 128, ad + 2 * k, bd + 2 * k, idesc_h, !(s == 0 && k == 0));
+                }
+                umma_commit(&empty[head_stage]);
+                umma_commit(&empty[head_stage + 1]);
                 umma_commit(mma_bar); dbg();
             }
         }
@@ -278,17 +300,13 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             if (lane == 0) mbar_arrive(epi_bar);
         };
         auto epi_sync = [&]() { asm volatile("bar.sync 1, 256;" ::: "memory"); };
-        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-            const int64_t m = (int64_t)t * 128 + row;
-            const int64_t mm = m < a.M ? m : a.M - 1;
-            const int64_t obj = mm / a.rows_per_obj;
-            const int64_t obj0 = ((int64_t)t * 128) / a.rows_per_obj;
-            const int64_t m_last = ((int64_t)t * 128 + 127 < a.M) ? (int64_t)t * 128 + 127 : a.M - 1;
-            const bool staged = (m_last / a.rows_per_obj) - obj0 <= 1;  // the tile touches at most two objects
-            const int64_t obj1 = obj0 + 1 < a.n_obj ? obj0 + 1 : obj0;
-            const float* base_obj = a.base + obj * ldbase;
-            // ---- tail k-block (slot 8): per-row inputs as [hi16 | lo16 | hi16 | 0] ----
-            if (half == 0) {
+        // ---- tail k-block (slot 8) of tile `tt`: per-row inputs as [hi16 | lo16 | hi16 | 0].  Done by the half-1 warps: for the first
+        // tile before the loop, afterwards during the head phase of the previous tile (slot 8 is free then, the half-0 warps are
+        // busy with the head epilogue), so the global loads of the next tile's inputs are off the critical path ----
+        auto pack_tail = [&](int tt) {
+            {
+                const int64_t m = (int64_t)tt * 128 + row;
+                const int64_t mm = m < a.M ? m : a.M - 1;
                 float v[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) v[j] = 0.f;
@@ -315,7 +333,18 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 for (int j = 0; j < 16; ++j) { w[16 + j] = 0.f; }
                 store_row32(slot, row, 4, w);  // chunks 4..7: hi | 0
             }
-            arrive_epi();
+        };
+        if (half == 1 && (int)blockIdx.x < ntiles) pack_tail((int)blockIdx.x);
+        arrive_epi();
+        for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            const int64_t m = (int64_t)t * 128 + row;
+            const int64_t mm = m < a.M ? m : a.M - 1;
+            const int64_t obj = mm / a.rows_per_obj;
+            const int64_t obj0 = ((int64_t)t * 128) / a.rows_per_obj;
+            const int64_t m_last = ((int64_t)t * 128 + 127 < a.M) ? (int64_t)t * 128 + 127 : a.M - 1;
+            const bool staged = (m_last / a.rows_per_obj) - obj0 <= 1;  // the tile touches at most two objects
+            const int64_t obj1 = obj0 + 1 < a.n_obj ? obj0 + 1 : obj0;
+            const float* base_obj = a.base + obj * ldbase;
             for (int b = 0; b < a.n_blocks; ++b) {
                 // ---- stage this block's per-object base rows and sh2 in shared memory (while the fc3 MMAs run) ----
                 epi_sync();  // every epilogue warp is done with the previous block's parameters
@@ -426,7 +455,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                     arrive_epi();
                 }
             }
-            // ---- heads ----
+            // ---- heads (half-0 warps) | next tile's tail pack (half-1 warps) ----
+            if (half == 1 && t + (int)gridDim.x < ntiles) pack_tail(t + (int)gridDim.x);
             wait_mma();
             if (half == 0) {
                 if (KIND == DEXGG_NET_GENERATOR) {
@@ -475,8 +505,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                     }
                 }
             }
-            // (no arrive here: the next tile's tail pack follows and arrives once for both)
-            tc_fence_before();
+            arrive_epi();  // head accumulators read, next tail packed: the MMA issuer may start the next tile
         }
     }
 
