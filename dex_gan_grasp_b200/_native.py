@@ -55,6 +55,9 @@ SIGNATURES = {
     "dexgg_magd_workspace_bytes": (c_size_t, [c_int]),
     "dexgg_magd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
                            c_void_p, c_void_p, c_size_t, c_void_p]),
+    "dexgg_part_rank_workspace_bytes": (c_size_t, [c_int64]),
+    "dexgg_part_rank": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                c_size_t, c_void_p]),
     "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
 }
 

@@ -253,7 +253,10 @@ class DexGanGrasp(object):
         return self.DexGANGrasp.generate_grasps(bps, n_samples, return_arr=return_arr, z_offset=z_offset)
 
     def refine_grasps(self, *a, **k):
-        raise NotImplementedError("refine_grasps: SURVEY.md §8f 'next'")
+        # Unreachable in the reference as well: no script calls it, and improve_grasps_gradient_based (dexgangrasp.py:516-541)
+        # raises on its first step - joint_conf is not an evaluator input (networks.py:307-313), so data['joint_conf'].grad is
+        # None at :539.  See DESIGN.md (§8f progress).
+        raise NotImplementedError("refine_grasps is dead code in the reference (joint_conf.grad is None there); not provided")
 
     # ------------------------------------------------------------------ checkpoints (:571-617,662-712)
     def load_dexevaluator(self, epoch, load_path=None):

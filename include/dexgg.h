@@ -203,6 +203,20 @@ int dexgg_magd(const float* pred_transl, const float* pred_rot, const float* pre
                const float* gt_rot, const float* gt_joint, int M, int n_joints, int32_t* match_out, float* per_grasp_out,
                double* sums_out, void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Part-conditioned ranking: the k grasps whose translation is nearest to the centroid of an object
+ * part.  Replaces filter_grasps_given_mask + sort_grasps (DexGanGrasp/utils/filter_grasps_given_mask.py:84-138;
+ * dexafford_prompt.py:191-192): part points are shifted by -pc_center, cropped to |x|,|y|,|z| < crop (0.2 in the reference),
+ * averaged; grasps are ordered by ascending squared distance of `transl` to that centroid.
+ *   transl [n_grasps,3], part_pts [n_part,3] f32 on the device; pc_center 3 floats on the HOST; n_grasps <= 16384
+ *   idx_out [k] i32 grasp rows, nearest first; neg_sqdist_out [k] f32 (may be NULL) = MINUS the squared distance of each;
+ *   centroid_out [3] f32 on the device (may be NULL; NaN when the crop leaves no point, like numpy's empty mean).
+ * ---------------------------------------------------------------------------------------------------------- */
+size_t dexgg_part_rank_workspace_bytes(int64_t n_grasps);
+int dexgg_part_rank(const float* transl, int64_t n_grasps, const float* part_pts, int64_t n_part, const float* pc_center,
+                    float crop, int k, int32_t* idx_out, float* neg_sqdist_out, float* centroid_out, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
 /* FP32-pipe micro-benchmark used for the BPS roofline denominator: runs `iters` rounds of 8
  * independent FFMA (kind 0), FFMA2 (kind 1), FADD2 (kind 2) or FMNMX3 (kind 3) chains per thread on a full grid and
  * returns the elapsed milliseconds in *ms and the number of lane-operations executed in *lane_ops. */
