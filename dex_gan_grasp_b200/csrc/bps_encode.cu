@@ -242,7 +242,7 @@ __device__ __forceinline__ f32x2 filter_a2(f32x2 nbx, f32x2 nby, f32x2 nbz, floa
 }
 
 template <int R>
-__global__ void __launch_bounds__(BPS_THREADS, 3)
+__global__ void __launch_bounds__(BPS_THREADS, R >= 16 ? 3 : (R >= 8 ? 5 : 7))
 bps_nn_filter_kernel(const float* __restrict__ basis, int P, const float* __restrict__ pts,
                      const int64_t* __restrict__ offsets, int64_t uniform_n, int64_t total_points, int nsplit,
                      unsigned long long* __restrict__ keys) {
@@ -627,7 +627,10 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
             bps_nn_scalar_kernel<<<grid, 128, 0, st>>>(basis, P, pts, offsets, max_cloud_points, keys); ::dexgg::count_launches(1);
             DEXGG_LAUNCH_OK("bps_nn_scalar_kernel");
         } else {
-            constexpr int R = 16;
+            // basis points per thread: 8 for the filter kernel (94 registers -> 5 CTAs / 20 warps per SM; measured 1.52 ms at C3
+            // against 1.65 ms for 16 and 1.55 ms for 4), 16 for the direct kernel as tuned in round 1
+            constexpr int RF = 8, RD = 16;
+            const int R = (flags & DEXGG_BPS_DIRECT) ? RD : RF;
             const int gx = (P + BPS_THREADS * R - 1) / (BPS_THREADS * R);
             int nsplit = (flags >> 8) & 0xff;
             if (nsplit == 0) {
@@ -642,8 +645,8 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
             }
             // the filtered kernel addresses chunks with 14 bits: at most 2^14 * 32 points per split
             const bool direct = (flags & DEXGG_BPS_DIRECT) || (max_cloud_points + nsplit - 1) / nsplit + 8 > (int64_t)16384 * BPSF_CHUNK;
-            int rc = direct ? launch_packed<R>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st)
-                            : launch_filter<R>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st);
+            int rc = direct ? launch_packed<RD>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st)
+                            : launch_filter<RF>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st);
             if (rc != DEXGG_OK) return rc;
         }
     }

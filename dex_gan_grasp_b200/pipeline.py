@@ -106,14 +106,19 @@ class GraspPipeline:
         if getattr(self, "_h2d", None) is None:
             self._h2d, self._d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         S = int(samples_per_object)
+        if getattr(self, "_pl_bufs", None) is None:
+            self._pl_bufs = {}    # rotating device input sets / pinned result buffers, kept across calls (keyed by shape below)
         d_in, h_out = [None, None], [None, None]
         done = [None, None]       # compute of the step that last used input set j has finished
         pending = None            # (event, host tensors, byte counts) of the previous step
         for i, (clouds_host, z_host) in enumerate(steps):
             j = i & 1
             if d_in[j] is None:
-                d_in[j] = (torch.empty(clouds_host.shape, dtype=torch.float32, device=dev),
-                           torch.empty(z_host.shape, dtype=torch.float32, device=dev))
+                key = ("in", j, tuple(clouds_host.shape), tuple(z_host.shape))
+                if key not in self._pl_bufs:
+                    self._pl_bufs[key] = (torch.empty(clouds_host.shape, dtype=torch.float32, device=dev),
+                                          torch.empty(z_host.shape, dtype=torch.float32, device=dev))
+                d_in[j] = self._pl_bufs[key]
             d_clouds, d_z = d_in[j]
             if done[j] is not None:
                 self._h2d.wait_event(done[j])
@@ -133,7 +138,11 @@ class GraspPipeline:
             done[j] = torch.cuda.Event()
             done[j].record(main)
             if h_out[j] is None:
-                h_out[j] = (torch.empty(packed.shape, dtype=torch.float32).pin_memory(), torch.empty(cnt.shape, dtype=torch.int32).pin_memory())
+                key = ("out", j, tuple(packed.shape))
+                if key not in self._pl_bufs:
+                    self._pl_bufs[key] = (torch.empty(packed.shape, dtype=torch.float32).pin_memory(),
+                                          torch.empty(cnt.shape, dtype=torch.int32).pin_memory())
+                h_out[j] = self._pl_bufs[key]
             self._d2h.wait_event(done[j])
             with torch.cuda.stream(self._d2h):
                 h_out[j][0].copy_(packed, non_blocking=True)
