@@ -368,7 +368,7 @@ def main():
                 "peak_source": pk_src + " bf16_tflops_sustained",
                 "traffic": {"unit": "MB per launch (ncu dram__bytes_read+write, profiles/r01e_chain_ncu_full.md)", "generator": 70.0, "evaluator": 62.4,
                             "algorithmic": "generator 20 B in (z) + 96 B out per grasp = 118.8 MB + weights; evaluator 48 B in + 4 B out = 53.2 MB + weights: "
-                                           "the generator's DRAM reads are below its inputs because z and the hoisted base stay in L2"}}
+                                           "measured DRAM traffic is BELOW the algorithmic bytes: part of z / rot / transl / joint is still resident in the 126 MB L2 when the kernel ends"}}
     else:
         roof = {"bound": "fp32", "kernel": "linear_simt_kernel (fp32 CUDA-core mode, all MLP layers)", "achieved": mlp_tflops,
                 "peak": fp32_tflops, "unit": "TFLOP/s", "frac": mlp_tflops / fp32_tflops,
