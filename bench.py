@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--workload", default="c3", choices=["c3", "train"],
                     help="c3 = the headline inference metric; train = secondary C5 line (GAN + evaluator training step, global batch 4096)")
     ap.add_argument("--batch", type=int, default=4096, help="global training batch (C5)")
+    ap.add_argument("--train-scaling", default="strong", choices=["strong", "weak"],
+                    help="C5: strong = the global batch is split over the GPUs (SURVEY 8e); weak = --batch rows on every GPU")
+    ap.add_argument("--no-graph", action="store_true", help="C5: issue the step eagerly instead of replaying the captured CUDA graph")
     return ap.parse_args()
 
 
@@ -178,11 +181,20 @@ def run_train(args, rank, world, local):
     model = DexGanGrasp(dict(TRAIN_CFG, gpu_ids=[local], precision=args.precision))
     model.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
     model.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
-    full = synth.synth_train_batch(args.batch, seed=11)
+    weak = args.train_scaling == "weak"
+    global_batch = args.batch * world if weak else args.batch
+    full = synth.synth_train_batch(global_batch, seed=11)
     mine = {k: v.to(dev) for k, v in dataparallel.shard(full, rank, world).items()}
     host = {k: v.pin_memory() for k, v in dataparallel.shard(full, rank, world).items()}
+    captured = None
+    if not args.no_graph:
+        from dex_gan_grasp_b200.graph_step import CapturedTrainStep
+        captured = CapturedTrainStep(model, mine, with_evaluator=True, is_train_gen=True, warmup=2)
 
     def step(src):
+        if captured is not None:  # static input buffers <- this step's batch (device copy, or H2D from pinned memory), one graph launch
+            l = captured(src)
+            return l, l
         b = {k: v.clone() if src is mine else v.to(dev, non_blocking=True) for k, v in src.items()}
         l1 = model.update_dexgangrasp(b, is_train_gen=True)
         l2 = model.update_dexevaluator(b)
@@ -207,6 +219,8 @@ def run_train(args, rank, world, local):
     e1.record()
     barrier()
     launches = (L.dexgg_launch_count() - n0) // max(args.steps, 1)
+    if captured is not None:  # replays do not pass through the host launch counter: the graph's own kernel-node count
+        launches = captured.kernels_per_replay
     clocks = sampler.stop()
     ms = e0.elapsed_time(e1) / args.steps
     t0 = time.perf_counter()
@@ -220,15 +234,16 @@ def run_train(args, rank, world, local):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     h2d = sum(v.numel() * v.element_size() for v in host.values())
     if rank == 0:
-        line = {"metric": "samples/sec (DexGenerator + Discriminator + DexEvaluator training step)", "value": args.batch / (float(t[0]) * 1e-3),
+        line = {"metric": "samples/sec (DexGenerator + Discriminator + DexEvaluator training step)", "value": global_batch / (float(t[0]) * 1e-3),
                 "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": float(t[0]),
-                "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "higher_is_better": True, "scaling": args.train_scaling, "vs_baseline": None,
                 "dtype": "f32 CUDA-core GEMMs" if args.precision == "fp32" else "bf16 tensor-core GEMMs / f32 accumulate, f32 master weights",
                 "data": "synthetic",
-                "config": {"workload": "C5 GAN + evaluator training step", "global_batch": args.batch, "rows_per_gpu": args.batch // world,
+                "config": {"workload": "C5 GAN + evaluator training step", "global_batch": global_batch, "rows_per_gpu": global_batch // world,
+                           "issue": "eager (one Python call per kernel)" if captured is None else "one captured CUDA graph per step (graph_step.CapturedTrainStep)",
                            "precision": args.precision, "optimizer": "Adam lr 1e-4 wd 5e-4 (fused multi-tensor kernel)",
                            "l2": "working set (activations + weights + Adam state, > 500 MB) exceeds L2"},
-                "e2e": {"value": args.batch / (float(t[1]) * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d * world,
+                "e2e": {"value": global_batch / (float(t[1]) * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d * world,
                         "d2h_bytes_per_step": 8, "ms_per_step": float(t[1])},
                 "gpu_launches": int(launches), "clocks": clocks, "last_loss": loss_host}
         print(json.dumps(line), flush=True)

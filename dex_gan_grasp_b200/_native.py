@@ -58,6 +58,7 @@ SIGNATURES = {
     "dexgg_part_rank_workspace_bytes": (c_size_t, [c_int64]),
     "dexgg_part_rank": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                 c_size_t, c_void_p]),
+    "dexgg_adam_step_dev": (c_int, [c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_void_p, c_void_p]),
     "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
 }
 

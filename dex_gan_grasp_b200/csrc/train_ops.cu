@@ -129,6 +129,33 @@ __global__ void adam_multi_kernel(const AdamChunk* __restrict__ chunks, float lr
     }
 }
 
+// Variant for a step captured in a CUDA graph: the step count lives in device memory (a kernel argument would be frozen at
+// capture time).  adam_step_inc_kernel bumps it, then every CTA derives the bias corrections from it in double precision.
+__global__ void adam_step_inc_kernel(int* step) { *step += 1; }
+
+__global__ void adam_multi_dev_kernel(const AdamChunk* __restrict__ chunks, float lr, float beta1, float beta2, float eps, float wd,
+                                      const int* __restrict__ step) {
+    __shared__ float s_bc[2];
+    if (threadIdx.x == 0) {
+        const int t = *step;
+        s_bc[0] = (float)(1.0 - pow((double)beta1, (double)t));
+        s_bc[1] = (float)sqrt(1.0 - pow((double)beta2, (double)t));
+    }
+    __syncthreads();
+    const float bc1 = s_bc[0], bc2_sqrt = s_bc[1];
+    const AdamChunk c = chunks[blockIdx.x];
+    for (int i = threadIdx.x; i < c.n; i += blockDim.x) {
+        const float w = c.w[i];
+        const float g = fmaf(wd, w, c.g[i]);
+        const float m = beta1 * c.m[i] + (1.f - beta1) * g;
+        const float v = beta2 * c.v[i] + (1.f - beta2) * g * g;
+        c.m[i] = m;
+        c.v[i] = v;
+        const float denom = sqrtf(v) / bc2_sqrt + eps;
+        c.w[i] = w - (lr / bc1) * (m / denom);
+    }
+}
+
 }  // namespace dexgg
 
 using namespace dexgg;
@@ -229,6 +256,21 @@ extern "C" int dexgg_bn_backward_apply(const float* g, int64_t ldg, const float*
     if (M == 0) return DEXGG_OK;
     bn_backward_apply_kernel<<<nb(M * N), 256, 0, static_cast<cudaStream_t>(stream)>>>(g, ldg, x, ldx, mean, invstd, gamma, sum_g, sum_gx, count, M, N, gx, ldo); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("bn_backward_apply_kernel");
+    return DEXGG_OK;
+}
+
+// Graph-capturable form of dexgg_adam_step: `step_dev` (device int, the number of steps taken so far) is incremented first and
+// the bias corrections are computed from it on the device.
+extern "C" int dexgg_adam_step_dev(const void* chunks_dev, int n_chunks, float lr, float beta1, float beta2, float eps,
+                                   float weight_decay, int* step_dev, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(n_chunks >= 0 && step_dev && (n_chunks == 0 || chunks_dev), "adam_step_dev: bad arguments");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    adam_step_inc_kernel<<<1, 1, 0, st>>>(step_dev); ::dexgg::count_launches(1);
+    DEXGG_LAUNCH_OK("adam_step_inc_kernel");
+    if (n_chunks == 0) return DEXGG_OK;
+    adam_multi_dev_kernel<<<n_chunks, 256, 0, st>>>(static_cast<const AdamChunk*>(chunks_dev), lr, beta1, beta2, eps, weight_decay, step_dev); ::dexgg::count_launches(1);
+    DEXGG_LAUNCH_OK("adam_multi_dev_kernel");
     return DEXGG_OK;
 }
 

@@ -334,7 +334,7 @@ class DexGanGrasp(object):
         self.DexEvaluator.train()
         out = self.DexEvaluator(data)
         total_loss_dexevaluator, loss_dict_dexevaluator = self.compute_loss_dexevaluator(out)
-        self.optim_dexevaluator.zero_grad()
+        self.optim_dexevaluator.zero_grad(set_to_none=getattr(self, '_zero_grad_to_none', True))
         total_loss_dexevaluator.backward()
         self._sync_grads(self.DexEvaluator)
         self.optim_dexevaluator.step()
@@ -363,7 +363,7 @@ class DexGanGrasp(object):
         real_score = D(real_data)
         fake_score = D(fake_data_disc)
         total_loss_disc, loss_dict_disc = self.compute_loss_dexgangrasp_discriminator(real_score, fake_score, real_data, fake_data_disc)
-        self.optim_dexgangrasp_discriminator.zero_grad()
+        self.optim_dexgangrasp_discriminator.zero_grad(set_to_none=getattr(self, '_zero_grad_to_none', True))
         total_loss_disc.backward()
         self._sync_grads(D)
         self.optim_dexgangrasp_discriminator.step()
@@ -383,7 +383,7 @@ class DexGanGrasp(object):
                     p.requires_grad_(True)
             real_data["rot_matrix"] = real_data["rot_matrix"].view(real_data["bps_object"].shape[0], -1)
             total_loss_gen, loss_dict_gen = self.compute_loss_dexgangrasp_generator(real_data, fake_data, fake_score_gen)
-            self.optim_dexgangrasp_generator.zero_grad()
+            self.optim_dexgangrasp_generator.zero_grad(set_to_none=getattr(self, '_zero_grad_to_none', True))
             total_loss_gen.backward()
             self._sync_grads(G)
             self.optim_dexgangrasp_generator.step()

@@ -1,0 +1,80 @@
+"""The training step as ONE CUDA graph: `update_dexgangrasp` (+ `update_dexevaluator`) of dexgangrasp.py:739-823 captured once
+and replayed per batch.
+
+The step is ~600 kernel launches (and, data parallel, ~80 small NCCL collectives) issued from Python; at 4096 / N rows per
+GPU the launches, not the kernels, bound the step.  Capturing it removes the host from the loop: static input
+buffers, the autograd forward / backward, the gradient and BatchNorm-statistics allreduces and the fused Adam kernels (step
+count in device memory, `dexgg_adam_step_dev`) all replay from one `cudaGraphLaunch`.
+
+    step = CapturedTrainStep(model, example_batch)        # 3 eager warm-up steps, then capture
+    losses = step(batch)                                   # dict of device tensors (valid until the next call)
+
+Numerics are those of the eager step (same kernels, same order).  Learning-rate changes made by the schedulers after the
+capture are NOT seen by the graph (lr is a kernel argument): re-capture after `update_learning_rate` changes a group.
+"""
+import torch
+
+from . import train_ops
+
+
+class CapturedTrainStep:
+    def __init__(self, model, example_batch, with_evaluator=True, is_train_gen=True, warmup=3, example_z=None):
+        if warmup < 1:
+            raise ValueError("at least one eager warm-up step is needed: it creates the Adam moments and the gradient buffers "
+                             "outside the capture (a zero-fill captured in the graph would reset the moments at every replay)")
+        self.model = model
+        self.with_evaluator = bool(with_evaluator)
+        self.is_train_gen = bool(is_train_gen)
+        dev = model.device
+        self.static = {k: (v.to(dev).clone() if torch.is_tensor(v) else v) for k, v in example_batch.items()}
+        # optional caller-supplied latent batch (parity tests); otherwise the step draws z from the CUDA generator in the graph
+        self.static_z = example_z.to(dev).clone() if example_z is not None else None
+        self.opts = [model.optim_dexgangrasp_discriminator] + ([model.optim_dexgangrasp_generator] if is_train_gen else []) + \
+                    ([model.optim_dexevaluator] if with_evaluator else [])
+        # gradients are zeroed in place instead of dropped, so their addresses (and with them the Adam chunk table built in the
+        # warm-up step) stay the same inside the capture: no host -> device table copy gets captured
+        model._zero_grad_to_none = False
+        for o in self.opts:
+            o.device_step = True
+            if getattr(o, "_step_dev", None) is None:  # device-side step counter, created outside the capture
+                taken = [int(st["step"]) for st in o.state.values() if "step" in st]
+                o._step_dev = torch.tensor([taken[0] if taken else 0], dtype=torch.int32, device=dev)
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        from . import _native
+        L = _native.lib()
+        n0 = L.dexgg_launch_count()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.losses = self._body()
+        self.kernels_per_replay = int(L.dexgg_launch_count() - n0)  # dexgg kernel nodes in the graph (host counter during capture)
+        for o in self.opts:  # the capture ran the Python side of the step (host counters + 1) without executing a kernel
+            for st in o.state.values():
+                if "step" in st:
+                    st["step"] -= 1
+        self.eager_steps = warmup
+
+    def _body(self):
+        b = dict(self.static)  # the step mutates the dict (rot_matrix view), never the static tensors
+        out = dict(self.model.update_dexgangrasp(b, is_train_gen=self.is_train_gen, Zgen=self.static_z))
+        if self.with_evaluator:
+            out.update(self.model.update_dexevaluator(dict(self.static)))
+        return {k: (v.detach() if torch.is_tensor(v) else v) for k, v in out.items()}
+
+    def __call__(self, batch, z=None):
+        for k, v in batch.items():
+            if torch.is_tensor(v):
+                self.static[k].copy_(v, non_blocking=True)
+        if z is not None:
+            self.static_z.copy_(z, non_blocking=True)
+        self.graph.replay()
+        for o in self.opts:  # keep torch.optim.Adam's host-side step counters (state_dict layout) in step with the device
+            for st in o.state.values():
+                if "step" in st:
+                    st["step"] += 1
+        return self.losses

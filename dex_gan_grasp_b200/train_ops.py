@@ -308,6 +308,7 @@ class DexggAdam(torch.optim.Adam):
     are torch's, so optimizer checkpoints written by the reference load unchanged."""
 
     CHUNK = 1 << 16
+    device_step = False  # True: the step count is kept in device memory too (dexgg_adam_step_dev), as CUDA-graph capture needs
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -343,13 +344,23 @@ class DexggAdam(torch.optim.Adam):
             key = tuple(chunks)
             if getattr(self, "_table_key", None) != key:  # chunk table lives on the device; rebuilt only when pointers move
                 arr = (_AdamChunk * len(chunks))(*[_AdamChunk(*c) for c in chunks])
-                self._table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(dev)
+                # pinned staging + async copy: legal inside a CUDA-graph capture (the pinned buffer is kept alive with the table)
+                self._table_host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).pin_memory()
+                self._table = self._table_host.to(dev, non_blocking=True)
                 self._table_key = key
             b1, b2 = group["betas"]
             lr = group["lr"]
+            step_now = steps.pop()
             with torch.cuda.device(dev):
-                _native.check(_L().dexgg_adam_step(self._table.data_ptr(), len(chunks), float(lr), float(b1), float(b2),
-                                                   float(group["eps"]), float(group["weight_decay"]), steps.pop(), _st(dev)))
+                if self.device_step:
+                    if getattr(self, "_step_dev", None) is None:  # created outside any capture (first, eager, step)
+                        self._step_dev = torch.tensor([step_now - 1], dtype=torch.int32, device=dev)
+                    _native.check(_L().dexgg_adam_step_dev(self._table.data_ptr(), len(chunks), float(lr), float(b1), float(b2),
+                                                           float(group["eps"]), float(group["weight_decay"]),
+                                                           self._step_dev.data_ptr(), _st(dev)))
+                else:
+                    _native.check(_L().dexgg_adam_step(self._table.data_ptr(), len(chunks), float(lr), float(b1), float(b2),
+                                                       float(group["eps"]), float(group["weight_decay"]), step_now, _st(dev)))
             # parameters changed behind torch's back: bump versions so packed inference weights refresh
             torch.autograd.graph.increment_version(params)
         return loss

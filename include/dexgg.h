@@ -188,6 +188,10 @@ int dexgg_bn_backward_apply(const float* g, int64_t ldg, const float* x, int64_t
                             float* gx, int64_t ldo, void* stream);
 int dexgg_adam_step(const void* chunks_dev, int n_chunks, float lr, float beta1, float beta2, float eps, float weight_decay,
                     int step, void* stream);
+/* Same update with the step count in DEVICE memory (`*step_dev` = steps taken so far; incremented by the call), so that a
+ * whole training step can be captured in a CUDA graph and replayed (graph_step.py). */
+int dexgg_adam_step_dev(const void* chunks_dev, int n_chunks, float lr, float beta1, float beta2, float eps,
+                        float weight_decay, int* step_dev, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * Mean Absolute Grasp Deviation between a predicted grasp set and a ground-truth set.

@@ -251,3 +251,49 @@ def test_bf16_training_reduces_the_loss(model_bf16):
         first = v if first is None else first
         last = v
     assert np.isfinite(last) and last < first, (first, last)
+
+
+def test_captured_step_equals_eager_steps():
+    """graph_step.CapturedTrainStep (the whole GAN + evaluator step as one CUDA graph, Adam step count on the device) against
+    the eager step from the same state on the same batches: identical kernels in identical order, so weights and BatchNorm
+    buffers must agree to fp32 atomics noise; dropout is off (p = 0) and z is supplied so that both sides are deterministic."""
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    from dex_gan_grasp_b200.graph_step import CapturedTrainStep
+
+    def fresh():
+        m = DexGanGrasp(dict(CFG))
+        m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+        m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+        m.DexEvaluator.dout.p = 0.0
+        return m
+
+    batches = [{k: v.cuda() for k, v in synth.synth_train_batch(B, seed=40 + i).items()} for i in range(6)]
+    zs = [synth.synth_latents(B, 5, seed=60 + i).cuda() for i in range(6)]
+    eager = fresh()
+    for i in [0] + list(range(6)):  # the captured side spends one eager warm-up step on the example batch first
+        b = {k: v.clone() for k, v in batches[i].items()}
+        le = dict(eager.update_dexgangrasp(b, Zgen=zs[i]))
+        le.update(eager.update_dexevaluator({k: v.clone() for k, v in batches[i].items()}))
+    torch.cuda.synchronize()
+    cap = fresh()
+    step = CapturedTrainStep(cap, batches[0], warmup=1, example_z=zs[0])  # one eager step on batch 0, then six replays
+    for i in range(6):
+        lc = step(batches[i], zs[i])
+    torch.cuda.synchronize()
+    for k in le:
+        assert abs(float(le[k]) - float(lc[k])) < 1e-4 * max(1.0, abs(float(le[k]))), (k, float(le[k]), float(lc[k]))
+    for name in ("DexGANGrasp", "DexEvaluator"):
+        sa, sb = getattr(eager, name).state_dict(), getattr(cap, name).state_dict()
+        params = {k for k, _ in getattr(eager, name).named_parameters()}
+        for k in sa:
+            if not sa[k].is_floating_point():
+                assert int(sa[k]) == int(sb[k]), (name, k)
+            elif k in params:
+                # Adam turns rounding noise in a near-zero gradient into up to a full step of lr (see _check_state): bounded
+                # by 2.1 * lr per step, and a small fraction of lr on average (atomics make two eager runs differ the same way)
+                d = (sa[k].double() - sb[k].double()).abs()
+                assert float(d.max()) <= 2.1e-4 * 7 and float(d.mean()) < 3e-5, (name, k, float(d.max()), float(d.mean()))
+            else:
+                assert md(sa[k], sb[k]) < 2e-4 * max(1.0, float(sa[k].abs().max())), (name, k, md(sa[k], sb[k]))
+    so = cap.optim_dexgangrasp_generator.state_dict()["state"]
+    assert all(int(s["step"]) == 7 for s in so.values())
