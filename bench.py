@@ -247,7 +247,13 @@ def run_train(args, rank, world, local):
                         "d2h_bytes_per_step": 8, "ms_per_step": float(t[1])},
                 "gpu_launches": int(launches), "clocks": clocks, "last_loss": loss_host}
         print(json.dumps(line), flush=True)
+    if captured is not None:
+        captured.close()
     if world > 1:
+        # the line is out; a communicator teardown that does not return (seen with captured collectives) must not hold the job
+        import threading
+        threading.Thread(target=lambda: (time.sleep(20), os._exit(0)), daemon=True).start()
+        dist.barrier()
         dist.destroy_process_group()
 
 

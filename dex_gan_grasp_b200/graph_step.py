@@ -78,3 +78,12 @@ class CapturedTrainStep:
                 if "step" in st:
                     st["step"] += 1
         return self.losses
+
+    def close(self):
+        """Destroy the graph (it holds references to the NCCL communicator's captured work: `destroy_process_group` must come
+        after this).  The model keeps training eagerly afterwards with the device-side step counters."""
+        torch.cuda.synchronize(self.model.device)
+        self.losses = None
+        if self.graph is not None:
+            self.graph.reset()
+            self.graph = None

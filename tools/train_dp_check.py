@@ -3,7 +3,9 @@
   torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/train_dp_check.py
 
 Every rank first runs the full-batch step alone (no process group), then the ranks run the sharded step with the NCCL
-gradient / BatchNorm-statistics exchange; losses, updated weights and BatchNorm running statistics must agree."""
+gradient / BatchNorm-statistics exchange; losses, updated weights and BatchNorm running statistics must agree.
+DP_GRAPH=1: the sharded side runs through graph_step.CapturedTrainStep (one eager warm-up step + one replay of the captured
+graph, NCCL collectives inside the graph) and the reference side takes the same two steps eagerly."""
 import copy, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -17,6 +19,7 @@ torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
 B = int(os.environ.get("DP_BATCH", "512"))
 prec = os.environ.get("DEXGG_PRECISION", "fp32")
+graph = os.environ.get("DP_GRAPH", "0") == "1"
 
 
 def fresh():
@@ -29,16 +32,24 @@ def fresh():
 full = synth.synth_train_batch(B, seed=11)
 z = synth.synth_latents(B, 5, seed=3)
 ref = fresh()
-lg = ref.update_dexgangrasp({k: v.to(dev) for k, v in full.items()}, is_train_gen=True, Zgen=z.to(dev))
+for _ in range(2 if graph else 1):
+    lg = ref.update_dexgangrasp({k: v.to(dev) for k, v in full.items()}, is_train_gen=True, Zgen=z.to(dev))
 torch.cuda.synchronize()
 
 dist.init_process_group("nccl", device_id=dev)
 dp = fresh()
 n = B // world
-lg2 = dp.update_dexgangrasp({k: v.to(dev) for k, v in dataparallel.shard(full, rank, world).items()}, is_train_gen=True,
-                            Zgen=z[rank * n:(rank + 1) * n].to(dev))
+mine = {k: v.to(dev) for k, v in dataparallel.shard(full, rank, world).items()}
+zmine = z[rank * n:(rank + 1) * n].to(dev)
+cap = None
+if graph:
+    from dex_gan_grasp_b200.graph_step import CapturedTrainStep
+    cap = CapturedTrainStep(dp, mine, with_evaluator=False, is_train_gen=True, warmup=1, example_z=zmine)
+    lg2 = cap(mine, z=zmine)
+else:
+    lg2 = dp.update_dexgangrasp(mine, is_train_gen=True, Zgen=zmine)
 torch.cuda.synchronize()
-out = {"world": world, "batch": B, "precision": prec, "loss_abs_diff": {}, "max_weight_diff": 0.0, "max_buffer_diff": 0.0}
+out = {"world": world, "batch": B, "precision": prec, "captured_graph": graph, "loss_abs_diff": {}, "max_weight_diff": 0.0, "max_buffer_diff": 0.0}
 for k in lg:
     # per-rank losses are means over the local shard: average them over ranks to compare with the full-batch mean
     t = torch.tensor([float(lg2[k])], device=dev, dtype=torch.float64)
@@ -60,4 +71,8 @@ dist.all_reduce(mn, op=dist.ReduceOp.MIN)
 out["max_rank_divergence"] = float((mx - mn).abs().max())
 if rank == 0:
     print(json.dumps(out), flush=True)
+if cap is not None:
+    cap.close()
+import threading, time
+threading.Thread(target=lambda: (time.sleep(20), os._exit(0)), daemon=True).start()
 dist.destroy_process_group()
