@@ -1,6 +1,6 @@
 """Host-side mirror of DexGanGrasp/models/dexgangrasp.py (class DexGanGrasp, :65-822): the same constructor, method names,
 arguments, returned dict keys, checkpoint layout and error behaviour; every forward / backward runs in libdexgg's
-sm_100a kernels.  WGAN-GP (is_wgan) and refine_grasps are "next" rows of SURVEY.md §8f and raise NotImplementedError.
+sm_100a kernels.  refine_grasps (dead code in the reference) raises NotImplementedError.
 """
 from __future__ import division
 
@@ -134,6 +134,71 @@ class DexGanGrasp(object):
         loss_dict = {'total_loss_eva': bce_loss_val, 'bce_loss': bce_loss_val}
         return bce_loss_val, loss_dict
 
+    # -- WGAN-GP variant (`is_wgan`, dexgangrasp.py:149-211,234-270) --
+    def calculate_interp(self, real_data, fake_data, alpha=None):
+        """dexgangrasp.py:149-158.  alpha ~ randn (NOT rand: reference quirk, kept); `alpha` lets a test supply it."""
+        if alpha is None:
+            shape = (real_data.size(0), 1, 1) if len(real_data.shape) == 3 else (real_data.size(0), 1)
+            alpha = torch.randn(shape, device=self.DexGANGrasp.device)
+        return (alpha * real_data + ((1 - alpha) * fake_data)).requires_grad_(True)
+
+    def calculate_grad_interp(self, interpolates, model_interpolates):
+        """dexgangrasp.py:160-173: d(sum of scores)/d(interpolates), kept in the graph for the second backward."""
+        grad_outputs = torch.ones(model_interpolates.size(), device=self.DexGANGrasp.device, requires_grad=False)
+        gradients = torch.autograd.grad(outputs=model_interpolates, inputs=interpolates, grad_outputs=grad_outputs,
+                                        create_graph=True, retain_graph=True, only_inputs=True)[0]
+        return gradients.view(gradients.size(0), -1)
+
+    def calculate_gradient_penalty(self, real_data, fake_data, alphas=None):
+        """dexgangrasp.py:175-202.  The interpolates go through the discriminator's twice-differentiable train-mode pass
+        (train_ops.discriminator_forward_double_backward: all GEMMs, of every derivative order, on the dexgg kernels)."""
+        dev = self.DexGANGrasp.device
+        names = ("rot_matrix", "transl", "joint_conf")
+        alphas = alphas if alphas is not None else (None, None, None)
+        interp_data = {"bps_object": real_data["bps_object"]}
+        for n, a in zip(names, alphas):
+            interp_data[n] = self.calculate_interp(real_data[n].to(dev), fake_data[n],
+                                                   None if a is None else a.to(dev))
+        D = self.DexGANGrasp.discriminator
+        D.double_backward = True
+        try:
+            interpolate_scores = D(interp_data)
+        finally:
+            D.double_backward = False
+        gradient_penalties = []
+        for out in names:
+            gradients = self.calculate_grad_interp(interp_data[out], interpolate_scores)
+            gradient_penalties.append(torch.mean((gradients.norm(2, dim=1) - 1) ** 2))
+        return torch.mean(torch.stack(gradient_penalties))
+
+    def compute_loss_dexgangrasp_discriminator_wass(self, real_score, fake_score, real_data, fake_data, penalty_gain=10,
+                                                    alphas=None):
+        """dexgangrasp.py:204-218 (the key names 'bce_loss_*' are the reference's, the values are mean scores)."""
+        bce_loss_real = torch.mean(real_score)
+        bce_loss_fake = torch.mean(fake_score)
+        gradient_penalty = self.calculate_gradient_penalty(real_data, fake_data, alphas)
+        total_loss_disc = -bce_loss_real + bce_loss_fake + (gradient_penalty * penalty_gain)
+        loss_dict = {'total_loss_disc': total_loss_disc, 'bce_loss_real': bce_loss_real, 'bce_loss_fake': bce_loss_fake}
+        return total_loss_disc, loss_dict
+
+    def compute_loss_dexgangrasp_generator_wass(self, real_data, fake_data, fake_score):
+        """dexgangrasp.py:234-270"""
+        dev = self.DexGANGrasp.device
+        gt = {'transl': real_data['transl'].to(dev).float(), 'rot_matrix': real_data['rot_matrix'].to(dev).float()}
+        transl_loss_val, rot_loss_val = self.rec_pose_loss(fake_data, gt, self.L2_loss, self.device)
+        conf_loss_val = self.L2_loss(fake_data['joint_conf'].to(dev).float(), real_data['joint_conf'].to(dev).float())
+        gen_loss_fake = - torch.mean(fake_score)
+        loss_dict = {
+            'gen_loss_fake': gen_loss_fake,
+            'transl_loss': self.transl_coef * transl_loss_val,
+            'rot_loss': self.rot_coef * rot_loss_val,
+            'conf_loss': self.conf_coef * conf_loss_val
+        }
+        total_loss = gen_loss_fake + (loss_dict['transl_loss'] + loss_dict['rot_loss'] + loss_dict['conf_loss'])
+        loss_dict["total_loss_gen"] = total_loss
+        self.last_loss_dict_gen = loss_dict
+        return total_loss, loss_dict
+
     def compute_loss_dexgangrasp_discriminator(self, real_score, fake_score, real_data=None, fake_data_disc=None):
         bce_loss_real = self.bce_weight * self.BCE_loss(real_score, torch.ones_like(real_score))
         bce_loss_fake = self.bce_weight * self.BCE_loss(fake_score, torch.zeros_like(fake_score))
@@ -183,9 +248,8 @@ class DexGanGrasp(object):
                          "transl": y_fake["transl"], "joint_conf": y_fake["joint_conf"]}
             fake_score_gen = self.DexGANGrasp.discriminator(fake_data)
             real_data["rot_matrix"] = real_data["rot_matrix"].view(real_data["bps_object"].shape[0], -1)
-            if self.is_wgan:
-                raise NotImplementedError("WGAN-GP variant: SURVEY.md §8f 'next'")
-            _, loss_dict_dexgenerator = self.compute_loss_dexgangrasp_generator(real_data, fake_data, fake_score_gen)
+            gen_loss = self.compute_loss_dexgangrasp_generator_wass if self.is_wgan else self.compute_loss_dexgangrasp_generator
+            _, loss_dict_dexgenerator = gen_loss(real_data, fake_data, fake_score_gen)
         return loss_dict_dexgenerator
 
     # ------------------------------------------------------------------ inference (:367-514)
@@ -345,10 +409,11 @@ class DexGanGrasp(object):
         from . import dataparallel
         dataparallel.allreduce_gradients(module)
 
-    def update_dexgangrasp(self, real_data, is_train_gen=True, Zgen=None):
-        """dexgangrasp.py:757-823 (non-WGAN branch).  `Zgen` (optional) lets a test supply the latent batch."""
-        if self.is_wgan:
-            raise NotImplementedError("WGAN-GP variant: SURVEY.md §8f 'next'")
+    def update_dexgangrasp(self, real_data, is_train_gen=True, Zgen=None, alphas=None):
+        """dexgangrasp.py:757-823, both loss selections (:761-763).  `Zgen` / `alphas` (optional) let a test supply the
+        latent batch and the three WGAN-GP interpolation weights."""
+        is_wgan = self.is_wgan
+        gen_loss = self.compute_loss_dexgangrasp_generator_wass if is_wgan else self.compute_loss_dexgangrasp_generator
         self._train_precision()
         self.DexGANGrasp.train()
         G, D = self.DexGANGrasp.generator, self.DexGANGrasp.discriminator
@@ -362,7 +427,11 @@ class DexGanGrasp(object):
                           "transl": fake_transl.detach(), "joint_conf": fake_joint_conf.detach()}
         real_score = D(real_data)
         fake_score = D(fake_data_disc)
-        total_loss_disc, loss_dict_disc = self.compute_loss_dexgangrasp_discriminator(real_score, fake_score, real_data, fake_data_disc)
+        if is_wgan:
+            total_loss_disc, loss_dict_disc = self.compute_loss_dexgangrasp_discriminator_wass(
+                real_score, fake_score, real_data, fake_data_disc, alphas=alphas)
+        else:
+            total_loss_disc, loss_dict_disc = self.compute_loss_dexgangrasp_discriminator(real_score, fake_score, real_data, fake_data_disc)
         self.optim_dexgangrasp_discriminator.zero_grad(set_to_none=getattr(self, '_zero_grad_to_none', True))
         total_loss_disc.backward()
         self._sync_grads(D)
@@ -382,7 +451,7 @@ class DexGanGrasp(object):
                 for p in d_params:
                     p.requires_grad_(True)
             real_data["rot_matrix"] = real_data["rot_matrix"].view(real_data["bps_object"].shape[0], -1)
-            total_loss_gen, loss_dict_gen = self.compute_loss_dexgangrasp_generator(real_data, fake_data, fake_score_gen)
+            total_loss_gen, loss_dict_gen = gen_loss(real_data, fake_data, fake_score_gen)
             self.optim_dexgangrasp_generator.zero_grad(set_to_none=getattr(self, '_zero_grad_to_none', True))
             total_loss_gen.backward()
             self._sync_grads(G)

@@ -247,6 +247,8 @@ class Discriminator(nn.Module):
         self.set_input(data)
         if self.training:
             from . import train_ops as T
+            if getattr(self, "double_backward", False):  # WGAN-GP interpolates pass (dexgangrasp.py:194)
+                return T.discriminator_forward_double_backward(self)
             return T.discriminator_forward_train(self)
         return self.native_forward(self.bps_object, self.rot_matrix, self.transl, self.joint_conf)
 

@@ -16,10 +16,12 @@ import ctypes
 
 import torch
 import torch.distributed as dist
+import torch.nn.functional as F
 
 from . import _native
 
 BN_EPS = 1e-5
+LRELU_SLOPE = 0.2  # networks.py:41
 
 
 def _L():
@@ -295,6 +297,71 @@ def evaluator_forward_train(eva, dropout_masks=None):
     X = dout(eva.rb2(torch.cat([X, X0], dim=1)), 1)
     X = dout(eva.rb3(torch.cat([X, X0], dim=1)), 2)
     return torch.sigmoid(linear(X, eva.out_success.weight, eva.out_success.bias))
+
+
+# ------------------------------------------------------------------------------ WGAN-GP: twice-differentiable D pass
+class _MatmulFn(torch.autograd.Function):
+    """C[M,N] = op(A) . op(W)^T on the dexgg GEMM (ta: A stored [K,M]; tw: W stored [K,N]).  Its backward is two more
+    _MatmulFn applications, so the op is differentiable to any order: the WGAN-GP gradient penalty
+    (dexgangrasp.py:160-202) differentiates the discriminator's input gradient w.r.t. its weights."""
+
+    @staticmethod
+    def forward(ctx, A, W, ta, tw):
+        _check_cuda(A)
+        A = _rowmajor(A)
+        W = _rowmajor(W)
+        K, M = (A.shape if ta else A.shape[::-1])
+        N = W.shape[1] if tw else W.shape[0]
+        ctx.ta, ctx.tw = int(ta), int(tw)
+        ctx.save_for_backward(A, W)
+        return raw_linear(A, int(ta), W, int(tw), M, N, K)
+
+    @staticmethod
+    def backward(ctx, G):
+        A, W = ctx.saved_tensors
+        ta, tw = ctx.ta, ctx.tw
+        gA = gW = None
+        if ctx.needs_input_grad[0]:  # dA'[m,k] = sum_n G[m,n] W'[n,k]   (stored transposed when ta)
+            gA = _MatmulFn.apply(W, G, 1 - tw, 0) if ta else _MatmulFn.apply(G, W, 0, 1 - tw)
+        if ctx.needs_input_grad[1]:  # dW'[n,k] = sum_m G[m,n] A'[m,k]   (stored transposed when tw)
+            gW = _MatmulFn.apply(A, G, 1 - ta, 1) if tw else _MatmulFn.apply(G, A, 1, 1 - ta)
+        return gA, gW, None, None
+
+
+def _linear_dd(x, lin, act=False):
+    y = _MatmulFn.apply(x, lin.weight, 0, 0) + lin.bias
+    return F.leaky_relu(y, LRELU_SLOPE) if act else y
+
+
+def _batch_norm_dd(x, bn):
+    """Train-mode BatchNorm1d with a double backward (torch's own batch_norm: elementwise / per-column glue between the
+    dexgg GEMMs).  Single process only: the cross-rank statistics exchange of _BatchNormFn has no second derivative."""
+    if _world() > 1:
+        raise NotImplementedError("dexgg: the WGAN-GP gradient-penalty pass is single-process (no cross-rank BatchNorm "
+                                  "statistics in the twice-differentiable path)")
+    y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, True,
+                     0.1 if bn.momentum is None else float(bn.momentum), BN_EPS)
+    if bn.num_batches_tracked is not None:
+        bn.num_batches_tracked += 1
+    return y
+
+
+def _resblock_dd(rb, x):
+    Xin = x if rb.Fin == rb.Fout else _linear_dd(x, rb.fc3, act=True)
+    h = F.leaky_relu(_batch_norm_dd(_linear_dd(x, rb.fc1), rb.bn1), LRELU_SLOPE)
+    h = _batch_norm_dd(_linear_dd(h, rb.fc2), rb.bn2)
+    return F.leaky_relu(Xin + h, LRELU_SLOPE)
+
+
+def discriminator_forward_double_backward(disc):
+    """Discriminator.forward (networks.py:148-159), train mode, as a graph torch can differentiate twice: every GEMM of
+    the forward, of the input-gradient pass and of the pass through that gradient runs on dexgg_linear_f32 / the
+    tcgen05 kernel via _MatmulFn; BatchNorm / LeakyReLU / sigmoid are torch element-wise ops."""
+    X = torch.cat([disc.bps_object, disc.rot_matrix, disc.transl, disc.joint_conf], dim=1)
+    X0 = _batch_norm_dd(X, disc.disc_bn1)
+    X = _resblock_dd(disc.disc_rb1, X0)
+    X = _resblock_dd(disc.disc_rb2, torch.cat([X0, X], dim=1))
+    return torch.sigmoid(_linear_dd(X, disc.out_success))
 
 
 # ---------------------------------------------------------------------------------------------------- optimizer

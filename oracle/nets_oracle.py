@@ -246,6 +246,76 @@ def gan_step(sd, opt_d, opt_g, batch, z, is_train_gen=True, bce_weight=1.0, lr=1
             sd[k].requires_grad_(False)
 
 
+def gradient_penalty(sd, bps, real, fake, alphas, prefix="discriminator."):
+    """DexGanGrasp.calculate_gradient_penalty (dexgangrasp.py:175-202) with calculate_interp (:149-158; alpha is drawn
+    with randn, NOT rand — reference quirk, kept) and calculate_grad_interp (:160-173).  `real` holds the batch's own
+    dtypes (float64 from the DataLoader), so the interpolates and their gradients are float64 like in the reference;
+    the discriminator casts to float32 (networks.py:136-139).  alphas = (a_rot [B,1,1], a_transl [B,1], a_joint [B,1])."""
+    names = ("rot_matrix", "transl", "joint_conf")
+    interp = {}
+    for n, a in zip(names, alphas):
+        interp[n] = (a * real[n] + ((1 - a) * fake[n])).requires_grad_(True)  # :157
+    score = discriminator_forward(sd, bps, interp["rot_matrix"].float(), interp["transl"].float(),
+                                  interp["joint_conf"].float(), training=True, prefix=prefix)  # :194
+    pens = []
+    for n in names:  # :197-200
+        g = torch.autograd.grad(score, interp[n], torch.ones_like(score), create_graph=True, retain_graph=True)[0]
+        g = g.view(g.size(0), -1)
+        pens.append(torch.mean((g.norm(2, dim=1) - 1) ** 2))
+    return torch.mean(torch.stack(pens))  # :202
+
+
+def wgan_step(sd, opt_d, opt_g, batch, z, alphas, is_train_gen=True, penalty_gain=10.0, lr=1e-4, beta1=0.9, wd=5e-4):
+    """DexGanGrasp.update_dexgangrasp (dexgangrasp.py:757-823), `is_wgan` branch: discriminator loss
+    -mean(D(real)) + mean(D(fake)) + 10*GP (:204-218; D keeps its sigmoid), generator loss -mean(D(fake)) + pose terms
+    (:234-270).  Same in-place conventions as gan_step."""
+    bps = batch["bps_object"].float()
+    rot = batch["rot_matrix"].float()
+    transl = batch["transl"].float()
+    joint = batch["joint_conf"].float()
+    gk = _params(sd, "generator.")
+    dk = _params(sd, "discriminator.")
+    for k in gk + dk:
+        sd[k].requires_grad_(True)
+    try:
+        fake = generator_forward(sd, z, bps, training=True)  # :772
+        fake_rot = rot_matrix_from_ortho6d(fake["rot_6D"])  # :776
+        fake_d = {"rot_matrix": fake_rot.detach(), "transl": fake["transl"].detach(), "joint_conf": fake["joint_conf"].detach()}
+        real_score = discriminator_forward(sd, bps, rot, transl, joint, training=True)  # :788
+        fake_score = discriminator_forward(sd, bps, fake_d["rot_matrix"], fake_d["transl"], fake_d["joint_conf"], training=True)
+        l_real = torch.mean(real_score)  # :206
+        l_fake = torch.mean(fake_score)
+        gp = gradient_penalty(sd, bps, batch, fake_d, alphas)  # :208
+        l_d = -l_real + l_fake + gp * penalty_gain  # :209
+        gd = torch.autograd.grad(l_d, [sd[k] for k in dk])
+        for k in gk + dk:
+            sd[k].requires_grad_(False)
+        adam_step(sd, dict(zip(dk, gd)), opt_d, lr, beta1, 0.999, 1e-8, wd)
+        losses = {"total_loss_disc": l_d.item(), "bce_loss_real": l_real.item(), "bce_loss_fake": l_fake.item(),
+                  "gradient_penalty": gp.item()}
+        grads = {"d": dict(zip(dk, gd))}
+        if is_train_gen:
+            for k in gk:
+                sd[k].requires_grad_(True)
+            score_gen = discriminator_forward(sd, bps, fake_rot, fake["transl"], fake["joint_conf"], training=True)  # :808
+            l_gen_fake = -torch.mean(score_gen)  # :258
+            l_t = 100.0 * F.mse_loss(fake["transl"], transl)
+            l_r = 1.0 * F.mse_loss(fake_rot.reshape(-1, 9), rot.reshape(-1, 9))
+            l_j = 10.0 * F.mse_loss(fake["joint_conf"], joint)
+            l_g = l_gen_fake + (l_t + l_r + l_j)  # :266
+            gg = torch.autograd.grad(l_g, [sd[k] for k in gk])
+            for k in gk:
+                sd[k].requires_grad_(False)
+            adam_step(sd, dict(zip(gk, gg)), opt_g, lr, beta1, 0.999, 1e-8, wd)
+            losses.update({"gen_loss_fake": l_gen_fake.item(), "transl_loss": l_t.item(), "rot_loss": l_r.item(),
+                           "conf_loss": l_j.item(), "total_loss_gen": l_g.item()})
+            grads["g"] = dict(zip(gk, gg))
+        return losses, grads
+    finally:
+        for k in gk + dk:
+            sd[k].requires_grad_(False)
+
+
 def evaluator_step(sd, opt, batch, dropout_masks=None, bce_weight=1.0, lr=1e-4, beta1=0.9, wd=5e-4):
     """DexGanGrasp.update_dexevaluator (dexgangrasp.py:739-755)."""
     keys = _params(sd)
