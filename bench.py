@@ -269,8 +269,6 @@ def main():
     if args.workload == "train":
         if not torch.cuda.is_available():
             raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
-        if "DEXGG_PRECISION" not in os.environ and "--precision" not in sys.argv:
-            args.precision = "fp32"
         run_train(args, rank, world, local)
         return
     import torch.distributed as dist

@@ -1,6 +1,6 @@
 """Host-side mirror of DexGanGrasp/models/dexgangrasp.py (class DexGanGrasp, :65-822): the same constructor, method names,
 arguments, returned dict keys, checkpoint layout and error behaviour; every forward / backward runs in libdexgg's
-sm_100a kernels.  refine_grasps (dead code in the reference) raises NotImplementedError.
+sm_100a kernels.  refine_grasps / improve_grasps_gradient_based run on the evaluator's input-gradient GEMMs.
 """
 from __future__ import division
 
@@ -316,11 +316,57 @@ class DexGanGrasp(object):
         """dexgangrasp.py:495-514"""
         return self.DexGANGrasp.generate_grasps(bps, n_samples, return_arr=return_arr, z_offset=z_offset)
 
-    def refine_grasps(self, *a, **k):
-        # Unreachable in the reference as well: no script calls it, and improve_grasps_gradient_based (dexgangrasp.py:516-541)
-        # raises on its first step - joint_conf is not an evaluator input (networks.py:307-313), so data['joint_conf'].grad is
-        # None at :539.  See DESIGN.md (§8f progress).
-        raise NotImplementedError("refine_grasps is dead code in the reference (joint_conf.grad is None there); not provided")
+    def improve_grasps_gradient_based(self, data, last_success):
+        """dexgangrasp.py:516-541: one gradient-ascent step on the evaluator score w.r.t. transl / rot_matrix, step length
+        capped so that transl moves <= 1 cm.  data['rot_matrix'] / data['transl'] are CUDA leaf tensors with
+        requires_grad (refine_grasps makes them); as in the reference their .grad is never zeroed, so step i moves along
+        the SUM of the gradients of steps 0..i.  DexEvaluator does not read joint_conf (networks.py:307-313), so
+        data['joint_conf'].grad stays None; the reference raises TypeError on that line (:539) - here it is the zero
+        gradient it mathematically is and joint_conf is left unchanged.  The reference's unused `diff` against
+        data['label'] (:528-529) is dropped, so no 'label' key is needed."""
+        from . import train_ops
+        self.DexEvaluator.eval()
+        bps = data['bps_object']
+        key = (bps.data_ptr(), tuple(bps.shape), bps._version, id(self.DexEvaluator))
+        if getattr(self, '_refine_graph', (None, None))[0] != key:
+            self._refine_graph = (key, train_ops.EvaluatorRefineGraph(self.DexEvaluator, bps.to(self.device, torch.float32)))
+        with train_ops.fp32_gemms():
+            p_success = self._refine_graph[1](data['rot_matrix'], data['transl'])
+            p_success.squeeze(-1).backward(torch.ones(p_success.shape[0], device=self.device))
+        norm_transl = torch.norm(data['transl'].grad, p=2, dim=-1)
+        alpha = torch.min(0.01 / norm_transl, torch.tensor(1.0, device=self.device))
+        data['transl'].data += data['transl'].grad * alpha[:, None]
+        data['rot_matrix'].data += data['rot_matrix'].grad * alpha[:, None, None]
+        if data['joint_conf'].grad is not None:
+            data['joint_conf'].data += data['joint_conf'].grad * alpha[:, None]
+        return p_success.squeeze(), None
+
+    def refine_grasps(self, data, refine_method, num_refine_steps=10, dtype=torch.float32):
+        """dexgangrasp.py:619-660: num_refine_steps evaluator-gradient steps on ranked grasps; returns (refined_data,
+        refined_success): the grasp dict as numpy arrays before every step and after the last one, and the scores before
+        every step plus the score of the final grasps.  refine_method 'gradient' only: the reference's sampling variant
+        (:543-569) reads attributes that do not exist (self.grasp_evaluator, utils.control_points_from_rot_and_trans)."""
+        from . import train_ops
+        if refine_method != "gradient":
+            raise NotImplementedError("refine_grasps: only refine_method='gradient'; the reference's sampling-based variant "
+                                      "(dexgangrasp.py:543-569) references attributes that do not exist")
+        data = {k: (v.to(dtype) if torch.is_tensor(v) else torch.as_tensor(v, dtype=dtype)) for k, v in data.items()}
+        data['bps_object'] = data['bps_object'].to(self.device).contiguous()
+        for k in ('rot_matrix', 'transl', 'joint_conf'):
+            data[k] = data[k].to(self.device).detach().clone().requires_grad_(True)
+
+        def as_numpy():
+            return {k: data[k].cpu().data.numpy() for k in ('rot_matrix', 'transl', 'joint_conf')}
+        refined_success, refined_data = [], [as_numpy()]
+        last_success = None
+        for _ in range(num_refine_steps):
+            p_success, last_success = self.improve_grasps_gradient_based(data, last_success)
+            refined_success.append(p_success.cpu().data.numpy())
+            refined_data.append(as_numpy())
+        with torch.no_grad(), train_ops.fp32_gemms():
+            refined_success.append(self._refine_graph[1](data['rot_matrix'], data['transl']).squeeze().cpu().numpy())
+        self._refine_graph = (None, None)
+        return refined_data, refined_success
 
     # ------------------------------------------------------------------ checkpoints (:571-617,662-712)
     def load_dexevaluator(self, epoch, load_path=None):

@@ -365,6 +365,76 @@ def discriminator_forward_double_backward(disc):
 
 
 # ---------------------------------------------------------------------------------------------------- optimizer
+# --------------------------------------------- evaluator-gradient grasp refinement (dexgangrasp.py:516-541, :619-660)
+class EvaluatorRefineGraph:
+    """Eval-mode DexEvaluator.forward (networks.py:315-337; BatchNorm on running statistics, Dropout inactive) as a graph
+    that autograd differentiates w.r.t. rot_matrix / transl - the quantity improve_grasps_gradient_based steps along.
+    The BPS columns of the three blocks' fc1 / fc3 products do not change while a grasp is refined, so they are computed
+    ONCE here (6 GEMMs of K = 4096); every refinement step then costs GEMMs of K = 12 and K = 512 only.  All GEMMs,
+    forward and input-gradient, are _MatmulFn -> dexgg_linear_f32 in fp32 (a <= 1 cm step along the gradient is only
+    meaningful at full precision); BatchNorm affines / LeakyReLU / sigmoid between them are torch element-wise ops."""
+
+    def __init__(self, eva, bps_object):
+        _check_cuda(bps_object)
+        bps = _rowmajor(bps_object.detach())
+        n, nb = bps.shape
+        nn_ = eva.out_success.weight.shape[1]
+        with torch.no_grad(), fp32_gemms():
+            s, t = _bn_affine(eva.bn1)
+            xb = bps * s[:nb] + t[:nb]
+            self.s_pose, self.t_pose = s[nb:].clone(), t[nb:].clone()
+            self.blocks = []
+            for rb, off in ((eva.rb1, 0), (eva.rb2, nn_), (eva.rb3, nn_)):
+                blk = {}
+                for name in ("fc1", "fc3"):
+                    lin = getattr(rb, name)
+                    W = lin.weight.detach()
+                    Wb = W[:, off:off + nb].contiguous()
+                    blk[name + "_base"] = raw_linear(xb, 0, Wb, 0, n, W.shape[0], nb, bias=lin.bias.detach())
+                    blk[name + "_Wp"] = W[:, off + nb:].contiguous()
+                    blk[name + "_Wx"] = W[:, :off].contiguous() if off else None
+                blk["s1"], blk["t1"] = _bn_affine(rb.bn1)
+                blk["s2"], blk["t2"] = _bn_affine(rb.bn2)
+                blk["t2"] = blk["t2"] + rb.fc2.bias.detach() * blk["s2"]
+                blk["W2"] = rb.fc2.weight.detach().contiguous()
+                self.blocks.append(blk)
+            self.Wout = eva.out_success.weight.detach().contiguous()
+            self.bout = eva.out_success.bias.detach().clone()
+
+    def __call__(self, rot_matrix, transl):
+        n = transl.shape[0]
+        with fp32_gemms():
+            pose = torch.cat([rot_matrix.reshape(n, -1), transl], dim=1) * self.s_pose + self.t_pose
+            X = None
+            for blk in self.blocks:
+                def lin(name):
+                    y = blk[name + "_base"] + _MatmulFn.apply(pose, blk[name + "_Wp"], 0, 0)
+                    return y if X is None else y + _MatmulFn.apply(X, blk[name + "_Wx"], 0, 0)
+                Xin = F.leaky_relu(lin("fc3"), LRELU_SLOPE)
+                h = F.leaky_relu(lin("fc1") * blk["s1"] + blk["t1"], LRELU_SLOPE)
+                h = _MatmulFn.apply(h, blk["W2"], 0, 0) * blk["s2"] + blk["t2"]
+                X = F.leaky_relu(Xin + h, LRELU_SLOPE)
+            return torch.sigmoid(_MatmulFn.apply(X, self.Wout, 0, 0) + self.bout)
+
+
+def _bn_affine(bn):
+    """Eval-mode BatchNorm1d as y = x * s + t."""
+    s = bn.weight.detach() / torch.sqrt(bn.running_var + bn.eps)
+    return s, bn.bias.detach() - bn.running_mean * s
+
+
+class fp32_gemms:
+    """Scope in which raw_linear uses the fp32 CUDA-core GEMM whatever cfg['precision'] says."""
+
+    def __enter__(self):
+        global _PRECISION
+        self.saved, _PRECISION = _PRECISION, "fp32"
+
+    def __exit__(self, *a):
+        global _PRECISION
+        _PRECISION = self.saved
+
+
 class _AdamChunk(ctypes.Structure):
     _fields_ = [("w", ctypes.c_void_p), ("g", ctypes.c_void_p), ("m", ctypes.c_void_p), ("v", ctypes.c_void_p), ("n", ctypes.c_int)]
 

@@ -332,3 +332,34 @@ def evaluator_step(sd, opt, batch, dropout_masks=None, bce_weight=1.0, lr=1e-4, 
             sd[k].requires_grad_(False)
     adam_step(sd, dict(zip(keys, g)), opt, lr, beta1, 0.999, 1e-8, wd)
     return {"total_loss_eva": loss.item(), "bce_loss": loss.item()}, dict(zip(keys, g))
+
+
+def refine_grasps_gradient(sd_eva, data, num_refine_steps=10):
+    """refine_grasps(refine_method='gradient') (dexgangrasp.py:619-660) -> improve_grasps_gradient_based (:516-541):
+    every step evaluates the eval-mode evaluator, back-propagates ones through p_success to the rot_matrix / transl
+    leaves WITHOUT zeroing their .grad (the reference never does: step i moves along the sum of the gradients of steps
+    0..i), alpha = min(0.01 / ||transl.grad||_2, 1) per grasp, transl += grad*alpha, rot_matrix += grad*alpha.
+    joint_conf is not an evaluator input (networks.py:307-313): its gradient is identically zero and it stays as given
+    (the reference raises TypeError at :539 because the .grad it reads there is None; tests/golden/make_refine_golden.py
+    runs the reference's method with that .grad pre-set to zeros).  Returns (refined_data, refined_success) as
+    refine_grasps does: num_refine_steps + 1 entries each."""
+    bps = data["bps_object"].float()
+    rot = data["rot_matrix"].float().clone().requires_grad_(True)
+    transl = data["transl"].float().clone().requires_grad_(True)
+    joint = data["joint_conf"].float().clone()
+
+    def snap():
+        return {"rot_matrix": rot.detach().numpy().copy(), "transl": transl.detach().numpy().copy(),
+                "joint_conf": joint.numpy().copy()}
+    refined_data, refined_success = [snap()], []
+    for _ in range(num_refine_steps):
+        p = evaluator_forward(sd_eva, bps, rot, transl, training=False)
+        p.squeeze(-1).backward(torch.ones(p.shape[0]))
+        alpha = torch.min(0.01 / torch.norm(transl.grad, p=2, dim=-1), torch.tensor(1.0))
+        transl.data += transl.grad * alpha[:, None]
+        rot.data += rot.grad * alpha[:, None, None]
+        refined_success.append(p.detach().squeeze().numpy().copy())
+        refined_data.append(snap())
+    with torch.no_grad():
+        refined_success.append(evaluator_forward(sd_eva, bps, rot, transl, training=False).squeeze().numpy().copy())
+    return refined_data, refined_success
