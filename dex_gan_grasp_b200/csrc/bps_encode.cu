@@ -422,6 +422,7 @@ bps_nn_filter_kernel(const float* __restrict__ basis, int P, const float* __rest
     const int lane = tid & 31, warp = tid >> 5;
     const int pblock = blockIdx.x * (BPS_THREADS * R);
     const int total_chunks = (int)((span + BPSF_CHUNK - 1) / BPSF_CHUNK);
+    const bool resident = ntiles <= 2;  // tile 0 is still in stage0 and tile 1 in stage1
     // per-lane best (distance bits, local point index) over chunk `ch`; strict < keeps the lower index on a tie
     auto lane_chunk = [&](int ch, float qx, float qy, float qz, uint32_t& bd, uint32_t& bi) {
         const int64_t gbase = g0 + (int64_t)ch * BPSF_CHUNK + lane;
@@ -466,6 +467,47 @@ bps_nn_filter_kernel(const float* __restrict__ basis, int P, const float* __rest
         }
         commit(p, bd, bi);
     };
+    if (resident) {
+        // The range's (at most two) tiles are still intact in the stages (valid points are never rewritten), so every THREAD
+        // finishes its own R basis points from shared memory: 32 points per candidate chunk, ~19 instructions per point and
+        // 32 basis points per warp in flight, against ~50 warp instructions per basis point (L2 loads, two REDUX, an atomic
+        // by one lane) for the warp-per-basis-point form below.  Lane L visits the chunk's points in the order L, L+1, ...
+        // (mod 32): chunks are 96 floats apart, so unrotated lanes would all hit the same bank.  The running minimum is the
+        // 64-bit (d2 bits, local index) key, which keeps the lowest index on a tie whatever the visiting order.
+        const uint32_t lo = (uint32_t)(r0 - g0), nvalid = (uint32_t)(r1 - r0);
+#pragma unroll 1
+        for (int r = 0; r < R; ++r) {
+            const int p = pbase + r * BPS_THREADS;
+            const uint32_t pk = s_pack[r * BPS_THREADS + tid];
+            const uint32_t cn = p < P ? (pk & 15u) : 0u;
+            if (cn == 1u || cn == 2u) {
+                const float qx = basis[3 * p], qy = basis[3 * p + 1], qz = basis[3 * p + 2];
+                unsigned long long bk = ~0ull;
+                auto thread_chunk = [&](uint32_t ch) {
+                    const uint32_t base = ch * BPSF_CHUNK;  // a chunk never straddles the two stages (BPS_TILE % BPSF_CHUNK == 0)
+                    const float* sp = ((base >= BPS_TILE) ? stage1 : stage0) + 3 * (base & (BPS_TILE - 1));
+#pragma unroll 8
+                    for (int i = 0; i < BPSF_CHUNK; ++i) {
+                        const uint32_t j = (uint32_t)(lane + i) & (BPSF_CHUNK - 1);
+                        const float df = search_d2(qx, qy, qz, sp[3 * j], sp[3 * j + 1], sp[3 * j + 2]);
+                        const uint32_t li = base + j;
+                        const uint32_t d = (li - lo < nvalid) ? __float_as_uint(df) : 0xffffffffu;
+                        const unsigned long long k = ((unsigned long long)d << 32) | li;
+                        bk = k < bk ? k : bk;
+                    }
+                };
+                if (cn == 2u) thread_chunk((pk >> 4) & 0x3fffu);
+                thread_chunk(pk >> 18);
+                // d2 >= 0, so its bits order like its value; bits above +inf are a NaN distance (or "no valid point"): no result
+                if ((uint32_t)(bk >> 32) <= 0x7f800000u)
+                    atomicMin(&keys[(size_t)b * P + p], (bk & 0xffffffff00000000ull) | (uint32_t)(g0 + (bk & 0xffffffffu) - o0));
+            }
+            // more than two candidate chunks (near-ties): the whole-range scan of that basis point is done by the warp together
+            for (unsigned ov = __ballot_sync(0xffffffffu, cn > 2u); ov; ov &= ov - 1)
+                one(r * BPS_THREADS + (tid & ~31) + (__ffs(ov) - 1));
+        }
+        return;
+    }
     for (int e = warp; e < BPS_THREADS * R; e += 2 * (BPS_THREADS / 32)) {
         const int e1 = e + BPS_THREADS / 32;
         const int p0 = pblock + e, p1 = pblock + e1;

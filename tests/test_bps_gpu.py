@@ -98,6 +98,29 @@ def test_filter_near_ties_and_off_centre_clouds(oracle_lib, bps_golden):
             assert np.array_equal(d[b], do), (flags, b)
 
 
+def test_shared_memory_finish_small_ranges(oracle_lib, bps_golden):
+    """Ranges of at most 2048 points (the C3 shape) finish their candidates from the shared-memory stages, one thread per
+    basis point in a rotated visiting order: exact ties (coarse grid, duplicates), a thin shell (more than two candidate
+    chunks -> whole-range fallback in that path), an off-centre cloud, sizes around the tile and chunk boundaries and
+    unaligned cloud starts (ragged offsets), all bit-exact with the oracle."""
+    rng = np.random.default_rng(23)
+    basis = bps_golden["basis"][:640]
+    grid = (rng.integers(-6, 6, (30, 3)) / 32.0).astype(np.float32)
+    u = rng.normal(size=(2048, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    shell = (basis.mean(0) + 0.05 * u * (1.0 + 1e-7 * rng.normal(size=(2048, 1)))).astype(np.float32)
+    far = (rng.normal(0, 0.05, (1500, 3)) + np.array([4.0, -7.0, 2.5])).astype(np.float32)
+    clouds = [grid[rng.integers(0, 30, 2047)], shell, far, rng.normal(0, 0.08, (1, 3)).astype(np.float32),
+              rng.normal(0, 0.08, (33, 3)).astype(np.float32), rng.normal(0, 0.08, (1023, 3)).astype(np.float32),
+              rng.normal(0, 0.08, (1025, 3)).astype(np.float32), rng.normal(0, 0.08, (2048, 3)).astype(np.float32)]
+    for flags in (0, NSPLIT(2)):
+        d, i = dev_encode(basis, clouds, flags)
+        for b, c in enumerate(clouds):
+            do, io = oracle_bps(oracle_lib, basis, c)
+            assert np.array_equal(i[b], io), (flags, b)
+            assert np.array_equal(d[b], do), (flags, b)
+
+
 def test_uniform_batch_and_large_cloud(oracle_lib, bps_golden):
     basis = bps_golden["basis"]
     clouds = synth.synth_clouds(6, 2048)
