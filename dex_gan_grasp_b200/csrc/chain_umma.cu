@@ -46,8 +46,12 @@ struct ChTile {
 
 __global__ void chain_pack_kernel(const ChTile* __restrict__ tiles, unsigned char* __restrict__ stream) {
     const ChTile t = tiles[blockIdx.x];
-    for (int e = threadIdx.x; e < t.tile_rows * 64; e += blockDim.x) {
-        const int r = e >> 6, c = e & 63;
+    // pad = 0: [tile_rows x 64] tile, 128-byte swizzle.  pad = 1 + h: K half h of a [256 x 64] tile as a [256 x 32] tile under the
+    // 64-byte swizzle (main layers: a ring stage is then one K half of an N = 256 operand and is consumed - and released - on
+    // its own, instead of waiting for the partner stage that holds the other 128 rows)
+    const int kw = t.pad ? 32 : 64, c_off = t.pad ? 32 * ((int)t.pad - 1) : 0;
+    for (int e = threadIdx.x; e < t.tile_rows * kw; e += blockDim.x) {
+        const int r = e / kw, cl = e % kw, c = cl + c_off;
         float v = 0.f;
         bool lo = false;
         if (t.mode == 0) {
@@ -66,7 +70,8 @@ __global__ void chain_pack_kernel(const ChTile* __restrict__ tiles, unsigned cha
         if (t.rowscale && r < t.nrows) v *= t.rowscale[t.row0 + r];
         __nv_bfloat16 hi = __float2bfloat16_rn(v);
         if (lo) hi = __float2bfloat16_rn(v - __bfloat162float(hi));
-        const uint64_t off = t.dst_off + (uint64_t)r * 128 + (uint64_t)((((c >> 3) ^ (r & 7)) << 4) + ((c & 7) << 1));
+        const uint64_t off = t.pad ? t.dst_off + (uint64_t)r * 64 + (uint64_t)((((cl >> 3) ^ ((r >> 1) & 3)) << 4) + ((cl & 7) << 1))
+                                   : t.dst_off + (uint64_t)r * 128 + (uint64_t)((((c >> 3) ^ (r & 7)) << 4) + ((c & 7) << 1));
         *reinterpret_cast<__nv_bfloat16*>(stream + off) = hi;
     }
 }
@@ -228,20 +233,21 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 umma_commit(&empty[stage]);
                 if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
             };
-            // two consecutive 16 KB ring stages (always an even / odd pair: every phase has an even tile count) form one
-            // [256 x 64] B tile: N = 256 halves the shared-memory operand traffic per MAC against N = 128
+            // one [256 x 64] B tile = two consecutive ring stages, each ONE K HALF ([256 x 32], 64-byte swizzle) of it: N = 256
+            // halves the shared-memory operand traffic per MAC against N = 128, and every stage is consumed and released on its
+            // own (two K = 16 MMAs) as soon as it lands
             auto mma_tile2 = [&](uint32_t d_col, int slot, bool first) {
-                mbar_wait(&full[stage], phase);
-                mbar_wait(&full[stage + 1], phase);
-                tc_fence_after();
-                const uint64_t ad = umma_desc_sw128_kmajor(sA_u + slot * CH_SLOT_BYTES);
-                const uint64_t bd = umma_desc_sw128_kmajor(sR_u + stage * CH_SLOT_BYTES);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + d_col, ad + 2 * k, bd + 2 * k, idesc256, !(first && k == 0));
-                umma_commit(&empty[stage]);
-                umma_commit(&empty[stage + 1]);
-                stage += 2;
-                if (stage == CH_STAGES) { stage = 0; phase ^= 1; }
+                for (int hk = 0; hk < 2; ++hk) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint64_t ad = umma_desc_sw128_kmajor(sA_u + slot * CH_SLOT_BYTES) + 4 * hk;
+                    const uint64_t bd = umma_desc_sw64_kmajor(sR_u + stage * CH_SLOT_BYTES);
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) umma_bf16(tmem_base + d_col, ad + 2 * k, bd + 2 * k, idesc256, !(first && hk == 0 && k == 0));
+                    umma_commit(&empty[stage]);
+                    if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
+                }
             };
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
                 for (int b = 0; b < a.n_blocks; ++b) {
@@ -553,12 +559,13 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
                   "chain_pack: unsupported network for the fused kernel");
     std::vector<ChTile> tiles;
     uint64_t off = 0;
-    auto push = [&](const float* src, int ld, int row0, int nrows, int col0, int mode, int tile_rows, const float* rowscale = nullptr) {
+    auto push = [&](const float* src, int ld, int row0, int nrows, int col0, int mode, int tile_rows, const float* rowscale = nullptr,
+                    uint32_t khalf = 0) {
         ChTile t;
         t.rowscale = rowscale;
-        t.src = src; t.ld = ld; t.row0 = row0; t.nrows = nrows; t.col0 = col0; t.mode = mode; t.tile_rows = tile_rows; t.pad = 0;
+        t.src = src; t.ld = ld; t.row0 = row0; t.nrows = nrows; t.col0 = col0; t.mode = mode; t.tile_rows = tile_rows; t.pad = khalf;
         t.dst_off = off;
-        off += (uint64_t)tile_rows * 128;
+        off += (uint64_t)tile_rows * (khalf ? 64 : 128);
         tiles.push_back(t);
     };
     for (int b = 0; b < s.n_blocks; ++b) {
@@ -567,14 +574,15 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
             for (int i = 0; i < nkb; ++i) {
                 const bool tail = (i == nkb - 1);
                 const int col0 = tail ? (s.has_x[b] ? 512 : 0) : ch_xcol(i);
-                for (int q = 0; q < nq; ++q) push(s.Wt[b], KT, row_base + q * 128, 128, col0, tail ? 1 : 0, 128, s.sc[b]);
+                for (int g = 0; g < nq / 2; ++g)
+                    for (int hk = 0; hk < 2; ++hk) push(s.Wt[b], KT, row_base + g * 256, 256, col0, tail ? 1 : 0, 256, s.sc[b], 1 + hk);
             }
         };
         first_layer(256, 4);  // fc3 rows 256..767
         first_layer(0, 2);    // fc1 rows 0..255
         for (int h = 0; h < 2; ++h)
             for (int kb = 0; kb < 4; ++kb)
-                for (int q = 0; q < 2; ++q) push(s.W2[b], 256, h * 256 + q * 128, 128, kb * 64, 0, 128, s.sc2[b]);
+                for (int hk = 0; hk < 2; ++hk) push(s.W2[b], 256, h * 256, 256, kb * 64, 0, 256, s.sc2[b], 1 + hk);
     }
     const int hr = ch_head_rows(s.kind);
     for (int i = 0; i < CH_HEAD_TILES; ++i) {

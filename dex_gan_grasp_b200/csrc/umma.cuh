@@ -32,6 +32,17 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_kmajor(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
+// same for rows of 32 bf16 (64 B) under the 64-byte swizzle (16-byte chunk index ^= (row >> 1) & 3): 8-row groups 512 B apart,
+// layout 4 = SWIZZLE_64B
+__device__ __forceinline__ uint64_t umma_desc_sw64_kmajor(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(512 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)4 << 61;
+    return d;
+}
 // ---- instruction descriptor, kind::f16: D = f32, A = B = bf16, both K-major, M x N ----
 //   [4,6) c_format 1 = F32   [7,10) a_format 1 = BF16   [10,13) b_format 1 = BF16   [15] a_major 0   [16] b_major 0
 //   [17,23) N >> 3           [24,29) M >> 4
