@@ -147,7 +147,9 @@ namespace dexgg {
 template <int KIND>
 __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainArgs a) {
     extern __shared__ unsigned char ch_smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ch_smem_raw) + 1023) & ~(uintptr_t)1023);
+    // 1024-byte alignment by an OFFSET into the __shared__ array (a pointer rebuilt from an integer loses its address space and
+    // every access to it becomes a generic LD / ST with 64-bit address arithmetic instead of LDS / STS)
+    unsigned char* smem = ch_smem_raw + ((1024u - (smem_u32(ch_smem_raw) & 1023u)) & 1023u);
     unsigned char* sA = smem;                 // 9 activation k-block slots
     unsigned char* sR = smem + CH_A_BYTES;    // weight ring
     uint64_t* bars = reinterpret_cast<uint64_t*>(sR + CH_STAGES * CH_SLOT_BYTES);
