@@ -37,7 +37,7 @@ struct UmmaParams {
 __global__ void __launch_bounds__(UM_THREADS, 1)
 linear_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW, const UmmaParams p) {
     extern __shared__ unsigned char um_smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(um_smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* smem = um_smem_raw + ((1024u - (smem_u32(um_smem_raw) & 1023u)) & 1023u);  // keeps the shared address space
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + UM_STAGES * UM_STAGE_BYTES);
     uint64_t* full = bars;                       // [STAGES]
     uint64_t* empty = bars + UM_STAGES;          // [STAGES]
