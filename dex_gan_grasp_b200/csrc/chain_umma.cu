@@ -401,11 +401,14 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                         e1(col_of(cc), ra);
                         tmem_ld_wait();
                         if (cc + 2 < 8) tmem_ld_32x32(tlane + half * 256 + col_of(cc + 2) * 32, ra);
+                        // The fc1 MMAs only need D[128,384) to have been READ (their operands are X and the weights) and never touch
+                        // the packed R columns: arrive as soon as this warp's last accumulator load has landed, so the hand-off and
+                        // the first MMAs run under the conversion / TMEM store of the last chunk.
+                        else arrive_epi();
                         e1(col_of(cc + 1), rb);
                     }
                 }
                 tmem_st_wait();
-                arrive_epi();
                 // ---- E2: H = bf16(lrelu(fc1 + base)) -> slots 0..3 (bn1 is folded into the weights and the base) ----
                 wait_mma();
                 {
@@ -462,10 +465,12 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                         if (c + 2 < 4) {
                             tmem_ld_32x32(t0 + (c + 2) * 32, ra);
                             tmem_ld_32x16(q0 + (c + 2) * 16, qa);
-                        }
+                        } else if (h == 0) {
+                            arrive_epi();  // the second fc2 half reads H (slots 0..3) and only needs D[128,384) read: start it under
+                        }                  // this warp's last chunk (its stores go to slots 4..7, fenced again by the h = 1 arrive)
                         e3(c + 1, rb, qb);
                     }
-                    arrive_epi();
+                    if (h == 1) arrive_epi();
                 }
             }
             // ---- heads (half-0 warps) | next tile's tail pack (half-1 warps) ----
