@@ -385,7 +385,7 @@ def main():
         roof = {"bound": "tensor", "kernel": "chain_umma_kernel<G>,<E> (fused whole-network tcgen05 bf16 kernels; executed-algorithm FLOP of the hoisted chain)", "achieved": mlp_tflops,
                 "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": mlp_tflops / pk["bf16_tflops_sustained"],
                 "peak_source": pk_src + " bf16_tflops_sustained",
-                "traffic": {"unit": "MB per launch (ncu dram__bytes_read+write, profiles/r01j_chain_ncu_full.md)", "generator": 71.6, "evaluator": 62.5,
+                "traffic": {"unit": "MB per launch (ncu dram__bytes_read+write, profiles/r01l_chain_ncu_full.md)", "generator": 69.8, "evaluator": 62.4,
                             "algorithmic": "generator 20 B in (z) + 96 B out per grasp = 118.8 MB + weights; evaluator 48 B in + 4 B out = 53.2 MB + weights: "
                                            "measured DRAM traffic is BELOW the algorithmic bytes: part of z / rot / transl / joint is still resident in the 126 MB L2 when the kernel ends"}}
     else:
