@@ -33,6 +33,11 @@ SIGNATURES = {
     "dexgg_discriminator_forward": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_int64,
                                             c_void_p, c_void_p, c_size_t, c_void_p]),
     "dexgg_filter_topk": (c_int, [c_void_p, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "dexgg_filter_topk_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "dexgg_filter_topk_ws": (c_int, [c_void_p, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_size_t, c_void_p]),
+    "dexgg_filter_topk_gather": (c_int, [c_void_p, c_int64, c_int64, c_float, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                                         c_void_p, c_void_p, c_void_p]),
     "dexgg_linear_f32": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "dexgg_linear_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

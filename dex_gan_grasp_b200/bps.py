@@ -111,23 +111,31 @@ class bps_torch:
 
 
 class BPSEncoder:
-    """DexGanGrasp.data.bps_encoder.BPSEncoder (bps_encoder.py:12-55): same constructor arguments, same
-    `encode_pcd_with_bps(pcd) -> np.float32 [4096]`, same `min < 0.1` assertion."""
+    """DexGanGrasp.data.bps_encoder.BPSEncoder (bps_encoder.py:12-55): same constructor `(cfg, bps_path, vis=False)` (the
+    device is cuda:cfg["gpu_ids"][0], :16-17), same static `generate_new_bps(base_path)`, same
+    `encode_pcd_with_bps(pcd) -> np.float32 [4096]`, same `min < 0.1` assertion.  `bps_path=None` loads the basis shipped with
+    this package (the reference's models/basis_point_set.npy); `vis` is accepted and ignored (Open3D windows are out of scope:
+    no graphics stack)."""
 
-    def __init__(self, cfg=None, bps_path=None, device="cuda"):
+    def __init__(self, cfg=None, bps_path=None, vis=False):
         if bps_path is None:
             bps_path = BASIS_PATH
         self.bps_np = np.load(bps_path)
-        self.bps = bps_torch(custom_basis=self.bps_np, device=device)
+        gpu = cfg["gpu_ids"][0] if (cfg is not None and "gpu_ids" in cfg and len(cfg["gpu_ids"])) else torch.cuda.current_device()
+        self.device = torch.device("cuda:{}".format(gpu))
+        self.bps = bps_torch(custom_basis=self.bps_np, device=self.device)
+        self.VISUALIZE = False
 
-    def generate_new_bps(self, path, n_points=4096, radius=0.2):
-        b = bps_torch(bps_type="random_uniform", n_bps_points=n_points, radius=radius, n_dims=3, device=self.bps.device)
-        np.save(path, to_np(b.bps[0]))
+    @staticmethod
+    def generate_new_bps(base_path, n_points=4096, radius=0.2):
+        """bps_encoder.py:22-26: a new uniform-in-ball basis saved as <base_path>/basis_point_set.npy."""
+        b = bps_torch(bps_type="random_uniform", n_bps_points=n_points, radius=radius, n_dims=3)
+        np.save(os.path.join(base_path, "basis_point_set.npy"), to_np(b.bps.squeeze()))
 
     def encode_pcd_with_bps(self, obj_pcd):
         pts = np.asarray(obj_pcd.points if hasattr(obj_pcd, "points") else obj_pcd)
         pc_tensor = torch.from_numpy(np.ascontiguousarray(pts))
         enc = self.bps.encode(pc_tensor)["dists"]
-        enc_np = enc.cpu().detach().numpy().squeeze()
-        assert enc_np.min() < 0.1, "The pcd might not be normalized"
-        return enc_np
+        enc_np = enc.cpu().detach().numpy()
+        assert enc_np.min() < 0.1, "The pcd might not be in centered in origin !"
+        return np.squeeze(enc_np)

@@ -12,6 +12,8 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libdexgg.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xptxas=-v"]
+if os.environ.get("DEXGG_DEBUG") == "1":  # timing experiments of DESIGN.md §4.2 (DEXGG_CHAIN_NOSTREAM / _CLOCKS, DEXGG_NO_CHAIN)
+    NVCC_FLAGS.append("-DDEXGG_DEBUG")
 
 
 def sources():

@@ -619,11 +619,8 @@ template <int R>
 static int launch_packed(const float* basis, int P, const float* pts, const int64_t* offsets, int B, int64_t uniform_n,
                          int64_t total, int nsplit, unsigned long long* keys, cudaStream_t st) {
     const size_t smem = 2 * BPS_STAGE_FLOATS * sizeof(float) + (size_t)R * BPS_THREADS * 8;
-    static bool attr_set = false;
-    if (!attr_set && smem > 48 * 1024) {
-        DEXGG_CUDA_OK(cudaFuncSetAttribute(bps_nn_packed_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    static std::atomic<unsigned long long> attr_mask{0};
+    if (smem > 48 * 1024) DEXGG_SMEM_OPT_IN(bps_nn_packed_kernel<R>, smem, attr_mask);
     dim3 grid((P + BPS_THREADS * R - 1) / (BPS_THREADS * R), B, nsplit);
     bps_nn_packed_kernel<R><<<grid, BPS_THREADS, smem, st>>>(basis, P, pts, offsets, uniform_n, total, nsplit, keys); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("bps_nn_packed_kernel");
@@ -634,11 +631,8 @@ template <int R>
 static int launch_filter(const float* basis, int P, const float* pts, const int64_t* offsets, int B, int64_t uniform_n,
                          int64_t total, int nsplit, unsigned long long* keys, cudaStream_t st) {
     const size_t smem = (2 * BPS_STAGE_FLOATS + BPSF_W_FLOATS) * sizeof(float) + (size_t)R * BPS_THREADS * 4;
-    static bool attr_set = false;
-    if (!attr_set && smem > 48 * 1024) {
-        DEXGG_CUDA_OK(cudaFuncSetAttribute(bps_nn_filter_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    static std::atomic<unsigned long long> attr_mask{0};
+    if (smem > 48 * 1024) DEXGG_SMEM_OPT_IN(bps_nn_filter_kernel<R>, smem, attr_mask);
     dim3 grid((P + BPS_THREADS * R - 1) / (BPS_THREADS * R), B, nsplit);
     bps_nn_filter_kernel<R><<<grid, BPS_THREADS, smem, st>>>(basis, P, pts, offsets, uniform_n, total, nsplit, keys); ::dexgg::count_launches(1);
     DEXGG_LAUNCH_OK("bps_nn_filter_kernel");

@@ -28,6 +28,11 @@ constexpr int CH_PARAM_FLOATS = 2 * 768 + 512;  // per block: hoisted base of th
 constexpr int CH_A_BYTES = CH_NSLOT * CH_SLOT_BYTES;
 constexpr int CH_SMEM_BYTES = CH_A_BYTES + CH_STAGES * CH_SLOT_BYTES + CH_PARAM_FLOATS * 4 + 256 + 1024;
 constexpr int CH_TAIL_SLOT = 8;
+#ifdef DEXGG_DEBUG
+constexpr bool CH_DEBUG = true;   // the DEXGG_CHAIN_NOSTREAM / DEXGG_CHAIN_CLOCKS experiments of DESIGN.md §4.2
+#else
+constexpr bool CH_DEBUG = false;  // release: the debug branches fold away
+#endif
 
 __host__ __device__ inline int ch_block_tiles(int has_x) { return has_x ? 70 : 22; }  // fc3 4/kb + fc1 2/kb + fc2 16
 __host__ __device__ inline int ch_head_rows(int kind) { return kind == DEXGG_NET_GENERATOR ? 32 : 16; }
@@ -191,7 +196,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 size_t off = 0;
                 for (int i = 0; i < n_main; ++i) {
                     mbar_wait(&empty[stage], phase ^ 1);
-                    if (a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
+                    if (CH_DEBUG && a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
                     mbar_expect_tx(&full[stage], CH_SLOT_BYTES);
                     bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, CH_SLOT_BYTES, &full[stage]); }
                     off += CH_SLOT_BYTES;
@@ -201,7 +206,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 // odd stage pair (n_main is even; the evaluator's 16 KB fill only the first stage).  (Issuing it one pair earlier,
                 // ahead of the last fc2 pair, was measured slower: it delays that pair and the head MMAs are not data-bound.)
                 for (int j = 0; j < 2; ++j) mbar_wait(&empty[stage + j], phase ^ 1);
-                if (a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
+                if (CH_DEBUG && a.debug_no_stream) { mbar_arrive(&full[stage]); } else {
                 mbar_expect_tx(&full[stage], CH_HEAD_TILES * HEAD_BYTES);
                 bulk_g2s(sR + stage * CH_SLOT_BYTES, src + off, CH_HEAD_TILES * HEAD_BYTES, &full[stage]); }
                 mbar_arrive(&full[stage + 1]);  // the pair's second barrier completes its phase too (parities stay in step)
@@ -217,7 +222,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             int stage = 0, phase = 0, ephase = 0, head_stage = 0, head_phase = 0;
             int dbg_n = 0;
             auto dbg = [&]() {
-                if (a.debug_clock && blockIdx.x == 0 && dbg_n < 256) a.debug_clock[dbg_n++] = clock64();
+                if (CH_DEBUG && a.debug_clock && blockIdx.x == 0 && dbg_n < 256) a.debug_clock[dbg_n++] = clock64();
             };
             auto wait_epi = [&]() {
                 mbar_wait(epi_bar, ephase);
@@ -297,7 +302,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
         int mphase = 0;
         int dbg_n = 0;
         auto dbg = [&]() {
-            if (a.debug_clock && blockIdx.x == 0 && warp == 2 && lane == 0 && dbg_n < 256) a.debug_clock[256 + dbg_n++] = clock64();
+            if (CH_DEBUG && a.debug_clock && blockIdx.x == 0 && warp == 2 && lane == 0 && dbg_n < 256) a.debug_clock[256 + dbg_n++] = clock64();
         };
         auto wait_mma = [&]() {
             mbar_wait(mma_bar, mphase);
@@ -609,20 +614,19 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
 
 int chain_forward(const ChainArgs& a, cudaStream_t st) {
     DEXGG_REQUIRE(a.M >= 1 && a.stream && a.base && a.rows_per_obj >= 1, "chain_forward: bad arguments");
-    static bool attr = false;
-    if (!attr) {
-        DEXGG_CUDA_OK(cudaFuncSetAttribute(chain_umma_kernel<DEXGG_NET_GENERATOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_BYTES));
-        DEXGG_CUDA_OK(cudaFuncSetAttribute(chain_umma_kernel<DEXGG_NET_EVALUATOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, CH_SMEM_BYTES));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr_g{0}, attr_e{0};
+    DEXGG_SMEM_OPT_IN(chain_umma_kernel<DEXGG_NET_GENERATOR>, CH_SMEM_BYTES, attr_g);
+    DEXGG_SMEM_OPT_IN(chain_umma_kernel<DEXGG_NET_EVALUATOR>, CH_SMEM_BYTES, attr_e);
     const int64_t ntiles = (a.M + 127) / 128;
+#ifdef DEXGG_DEBUG  // timing experiments only (never in a release build): weight stream off / phase timeline of CTA 0
     { const char* e = getenv("DEXGG_CHAIN_NOSTREAM"); const_cast<ChainArgs&>(a).debug_no_stream = (e && e[0] == '1') ? 1 : 0; }
     static long long* dbg_buf = nullptr;
-    if (getenv("DEXGG_CHAIN_CLOCKS")) {  // timing experiment: dump the phase timeline of CTA 0 after the launch
+    if (getenv("DEXGG_CHAIN_CLOCKS")) {
         if (!dbg_buf) DEXGG_CUDA_OK(cudaMalloc(&dbg_buf, 512 * sizeof(long long)));
         DEXGG_CUDA_OK(cudaMemsetAsync(dbg_buf, 0, 512 * sizeof(long long), st));
         const_cast<ChainArgs&>(a).debug_clock = dbg_buf;
     }
+#endif
     const int grid = (int)(ntiles < sm_count() ? ntiles : sm_count());
     if (a.kind == DEXGG_NET_GENERATOR) {
         DEXGG_REQUIRE(a.z && a.rot && a.transl && a.joint && a.zD >= 1 && a.zD <= 16 && a.nh <= 32 && a.nJ + 9 == a.nh, "chain_forward: bad generator arguments");
@@ -633,6 +637,7 @@ int chain_forward(const ChainArgs& a, cudaStream_t st) {
     }
     count_launches(1);
     DEXGG_LAUNCH_OK("chain_umma_kernel");
+#ifdef DEXGG_DEBUG
     if (a.debug_clock) {
         std::vector<long long> h(512);
         DEXGG_CUDA_OK(cudaMemcpy(h.data(), dbg_buf, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
@@ -647,6 +652,7 @@ int chain_forward(const ChainArgs& a, cudaStream_t st) {
             fclose(f);
         }
     }
+#endif
     return DEXGG_OK;
 }
 

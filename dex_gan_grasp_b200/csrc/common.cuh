@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <stdarg.h>
 
+#include <atomic>
+
 #include "../../include/dexgg.h"
 
 namespace dexgg {
@@ -47,6 +49,18 @@ void count_launches(int n);         // kernels launched by this library (dexgg_l
     } while (0)
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute: opt in once per device ordinal (bit mask, thread
+// safe; setting it twice is harmless).  `mask` is one static std::atomic<unsigned long long> per kernel.
+#define DEXGG_SMEM_OPT_IN(func, bytes, mask)                                                                   \
+    do {                                                                                                       \
+        int _dev = 0;                                                                                          \
+        DEXGG_CUDA_OK(cudaGetDevice(&_dev));                                                                   \
+        if (_dev >= 64 || !((mask.load(std::memory_order_acquire) >> _dev) & 1ull)) {                          \
+            DEXGG_CUDA_OK(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes))); \
+            if (_dev < 64) mask.fetch_or(1ull << _dev, std::memory_order_release);                             \
+        }                                                                                                      \
+    } while (0)
 
 #ifdef __CUDACC__
 // ---- packed fp32x2 arithmetic (Blackwell FADD2 / FMUL2 / FFMA2): each half is an IEEE-754 round-to-nearest op ----

@@ -274,11 +274,8 @@ int linear_bf16(const LinearB16& q, cudaStream_t st) {
     int rc = make_tmap_bf16(&tmA, q.A, q.M, q.K, q.lda, UM_BM);
     if (rc) return rc;
     if ((rc = make_tmap_bf16(&tmW, q.W, q.N, q.K, q.ldw, BN))) return rc;
-    static bool attr = false;
-    if (!attr) {
-        DEXGG_CUDA_OK(cudaFuncSetAttribute(linear_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, UM_SMEM_BYTES));
-        attr = true;
-    }
+    static std::atomic<unsigned long long> attr_mask{0};
+    DEXGG_SMEM_OPT_IN(linear_umma_kernel, UM_SMEM_BYTES, attr_mask);
     UmmaParams p;
     p.M = q.M; p.N = q.N; p.K = q.K; p.BN = BN; p.ep = q.ep; p.ep.residual = nullptr;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(q.residual16); p.ldr = q.ldr;

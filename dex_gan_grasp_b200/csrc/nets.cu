@@ -424,14 +424,18 @@ void carve_net(dexgg_net* n, Carver& c) {
     }
 }
 
-// DEXGG_NO_CHAIN=1 forces the layer-by-layer tensor-core path (A/B measurements, cross-checks)
+// Debug builds only: DEXGG_NO_CHAIN=1 forces the layer-by-layer tensor-core path (A/B measurements, cross-checks)
 bool chain_enabled() {
+#ifdef DEXGG_DEBUG
     static int v = -1;
     if (v < 0) {
         const char* e = getenv("DEXGG_NO_CHAIN");
         v = (e && e[0] == '1') ? 0 : 1;
     }
     return v == 1;
+#else
+    return true;
+#endif
 }
 
 void chain_common(const dexgg_net* n, ChainArgs& a, const float* base, int64_t n_obj, int64_t rows_per_obj, int64_t M) {

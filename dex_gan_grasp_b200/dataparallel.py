@@ -14,6 +14,25 @@ def is_parallel():
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
 
+# Every collective of the training step goes through all_reduce_sum, which counts calls and bytes per kind ("grad",
+# "bn_fwd", "bn_bwd"): bench.py reports them per step (the host counters also advance during a CUDA-graph capture, which is
+# how CapturedTrainStep knows what one replay holds).
+_COUNTERS = {"grad_calls": 0, "grad_bytes": 0, "bn_fwd_calls": 0, "bn_fwd_bytes": 0, "bn_bwd_calls": 0, "bn_bwd_bytes": 0}
+
+
+def collective_counters():
+    return dict(_COUNTERS)
+
+
+def all_reduce_sum(t, kind="grad", async_op=False):
+    """Sum `t` over all ranks in place (no-op on one rank)."""
+    if not is_parallel():
+        return None
+    _COUNTERS[kind + "_calls"] += 1
+    _COUNTERS[kind + "_bytes"] += t.numel() * t.element_size()
+    return dist.all_reduce(t, op=dist.ReduceOp.SUM, async_op=async_op)
+
+
 def allreduce_gradients(module):
     """Average the gradients of `module` over all ranks with a single flat allreduce."""
     if not is_parallel():
@@ -22,7 +41,7 @@ def allreduce_gradients(module):
     if not params:
         return
     flat = torch.cat([p.grad.reshape(-1) for p in params])
-    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    all_reduce_sum(flat, "grad")
     flat.div_(dist.get_world_size())
     off = 0
     for p in params:

@@ -287,9 +287,12 @@ class DexGanGrasp(object):
         idx = torch.empty((n,), dtype=torch.int32, device=self.device)
         cnt = torch.empty((1,), dtype=torch.int32, device=self.device)
         best = torch.empty((1,), dtype=torch.float32, device=self.device)
+        L = _native.lib()
+        nws = L.dexgg_filter_topk_workspace_bytes(n, n)  # 0 up to 16384 grasps; longer lists sort in a workspace
+        ws = torch.empty((max(nws, 1),), dtype=torch.uint8, device=self.device)
         with torch.cuda.device(self.device):
-            _native.check(_native.lib().dexgg_filter_topk(p_success.data_ptr(), n, n, float(thresh), n, idx.data_ptr(),
-                                                          cnt.data_ptr(), best.data_ptr(), None, _native.stream_ptr(self.device)))
+            _native.check(L.dexgg_filter_topk_ws(p_success.data_ptr(), n, n, float(thresh), n, idx.data_ptr(), cnt.data_ptr(),
+                                                 best.data_ptr(), None, ws.data_ptr(), ws.numel(), _native.stream_ptr(self.device)))
         best_score, kept = float(best.item()), int(cnt.item())
         if best_score < thresh:
             raise ValueError("In total predicted ", n, " grasps, but best score ", best_score, " is still lower than thresh", thresh)

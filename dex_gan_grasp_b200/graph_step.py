@@ -48,16 +48,22 @@ class CapturedTrainStep:
         torch.cuda.synchronize(dev)
         from . import _native
         L = _native.lib()
+        from . import dataparallel
         n0 = L.dexgg_launch_count()
+        c0 = dataparallel.collective_counters()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.losses = self._body()
         self.kernels_per_replay = int(L.dexgg_launch_count() - n0)  # dexgg kernel nodes in the graph (host counter during capture)
+        c1 = dataparallel.collective_counters()
+        self.collectives_per_replay = {k: c1[k] - c0[k] for k in c1}  # NCCL collectives (calls / bytes per kind) in the graph
         for o in self.opts:  # the capture ran the Python side of the step (host counters + 1) without executing a kernel
             for st in o.state.values():
                 if "step" in st:
                     st["step"] -= 1
         self.eager_steps = warmup
+        mods = [model.DexGANGrasp] + ([model.DexEvaluator] if self.with_evaluator else [])
+        self._trained_tensors = [t for m in mods for t in list(m.parameters()) + list(m.buffers()) if t.is_floating_point()]
 
     def _body(self):
         b = dict(self.static)  # the step mutates the dict (rot_matrix view), never the static tensors
@@ -77,6 +83,9 @@ class CapturedTrainStep:
             for st in o.state.values():
                 if "step" in st:
                     st["step"] += 1
+        # the replay rewrote weights and BatchNorm buffers on the device behind torch's back: bump their version counters so
+        # the packed eval-mode copies (networks.NativeNet.sync) are rebuilt by the next eval-mode forward
+        torch.autograd.graph.increment_version(self._trained_tensors)
         return self.losses
 
     def close(self):

@@ -35,7 +35,7 @@ class GraspPipeline:
     def run_device(self, clouds, z, samples_per_object, z_ready=None):
         """clouds [B,N,3], z [B*S,latentD] on the device.  Returns a dict of device tensors:
         idx [B,k] i32 (global row ids, -1 padded), count [B], score [B,k], rot_matrix [B,k,3,3], transl [B,k,3],
-        joint_conf [B,k,nJ] (rows beyond count are zero)."""
+        joint_conf [B,k,nJ] (views of `packed`; rows beyond count are zero), bps [B,4096], p [M,1]."""
         S = int(samples_per_object)
         B = clouds.shape[0]
         M = B * S
@@ -48,27 +48,25 @@ class GraspPipeline:
         rot, transl, joint, _ = self.gan.generator.native_forward(z, enc, self.z_offset, False)
         p = self.eva.native_forward(enc, rot, transl)
         k = min(self.k, S)
+        nJ = joint.shape[1]
         idx = torch.empty((B, k), dtype=torch.int32, device=dev)
         cnt = torch.empty((B,), dtype=torch.int32, device=dev)
-        score = torch.empty((B, k), dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
-            _native.check(L.dexgg_filter_topk(p.data_ptr(), M, S, self.thresh, k, idx.data_ptr(), cnt.data_ptr(), None,
-                                              score.data_ptr(), _native.stream_ptr(dev)))
-        sel = idx.clamp_min(0).long().reshape(-1)
-        valid = (idx >= 0).reshape(-1, 1).float()
-        out = {
-            "idx": idx, "count": cnt, "score": score,
-            "rot_matrix": (rot.reshape(M, 9).index_select(0, sel) * valid).reshape(B, k, 3, 3),
-            "transl": (transl.index_select(0, sel) * valid).reshape(B, k, 3),
-            "joint_conf": (joint.index_select(0, sel) * valid).reshape(B, k, -1),
-            "bps": enc, "p": p,
+        packed = torch.empty((B, k, 14 + nJ), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):  # threshold + per-object top-k + gather of the kept rows: one launch (filter_topk.cu)
+            _native.check(L.dexgg_filter_topk_gather(p.data_ptr(), M, S, self.thresh, k, rot.data_ptr(), transl.data_ptr(),
+                                                     joint.data_ptr(), nJ, idx.data_ptr(), cnt.data_ptr(), packed.data_ptr(),
+                                                     _native.stream_ptr(dev)))
+        return {
+            "idx": idx, "count": cnt, "packed": packed,  # packed [B,k,14+nJ]: score | row id (int32 bits) | rot 9 | transl 3 | joints
+            "score": packed[:, :, 0], "rot_matrix": packed[:, :, 2:11].unflatten(2, (3, 3)), "transl": packed[:, :, 11:14],
+            "joint_conf": packed[:, :, 14:], "bps": enc, "p": p,
         }
-        return out
 
     # ------------------------------------------------------------------ host-buffer path (the e2e number of bench.py)
     def run_host(self, clouds_host, z_host, samples_per_object):
         """clouds_host / z_host: pinned CPU tensors.  Copies them to the device, runs the path and reads the top-k result
-        back to the host (one packed [B,k,26+nJ... ] block + counts).  Returns (dict of CPU tensors, h2d bytes, d2h bytes)."""
+        back to the host (one packed [B,k,14+nJ] block: score | row id as int32 bits | rot 9 | transl 3 | joints, + counts;
+        `unpack_host` splits it).  Returns (dict of CPU tensors, h2d bytes, d2h bytes)."""
         dev = self.device
         key = (tuple(clouds_host.shape), tuple(z_host.shape))
         if key not in self._stage:
@@ -86,9 +84,7 @@ class GraspPipeline:
             z_ready = torch.cuda.Event()
             z_ready.record(self._copy_stream)
         out = self.run_device(d_clouds, d_z, samples_per_object, z_ready=z_ready)
-        B, k = out["idx"].shape
-        packed = torch.cat([out["score"].reshape(B, k, 1), out["idx"].float().reshape(B, k, 1), out["rot_matrix"].reshape(B, k, 9),
-                            out["transl"], out["joint_conf"]], dim=2)
+        packed = out["packed"]
         host = packed.cpu()  # synchronising D2H read of the result
         cnt = out["count"].cpu()
         h2d = clouds_host.numel() * 4 + z_host.numel() * 4
@@ -131,9 +127,7 @@ class GraspPipeline:
                 ready.record(self._h2d)
             main.wait_event(ready)
             out = self.run_device(d_clouds, d_z, S)
-            B, k = out["idx"].shape
-            packed = torch.cat([out["score"].reshape(B, k, 1), out["idx"].float().reshape(B, k, 1), out["rot_matrix"].reshape(B, k, 9),
-                                out["transl"], out["joint_conf"]], dim=2)
+            packed = out["packed"]
             cnt = out["count"]
             done[j] = torch.cuda.Event()
             done[j].record(main)
@@ -160,3 +154,13 @@ class GraspPipeline:
         if pending is not None:
             pending[0].synchronize()
             yield pending[1], pending[2], pending[3]
+
+
+def unpack_host(packed, count=None):
+    """Splits a packed result block (CPU or device tensor [B,k,14+nJ]) into named views; row ids come back exact (int32)."""
+    ids = packed.view(torch.int32)[:, :, 1]
+    out = {"score": packed[:, :, 0], "idx": ids, "rot_matrix": packed[:, :, 2:11].unflatten(2, (3, 3)),
+           "transl": packed[:, :, 11:14], "joint_conf": packed[:, :, 14:]}
+    if count is not None:
+        out["count"] = count
+    return out

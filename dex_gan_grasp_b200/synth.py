@@ -180,6 +180,29 @@ def synth_clouds(n_clouds, n_points, seed0=1000):
     return out
 
 
+_BASE_SHAPES = {}
+
+
+def synth_clouds_by_id(ids, n_points, seed0=1000):
+    """[len(ids),N,3] float32 clouds addressed by GLOBAL object id: ids < 64 are the distinct shapes synth_cloud(seed0 + id);
+    id >= 64 re-poses shape id % 64 with a rotation / permutation / scale drawn from a generator seeded by the id itself, so
+    an object's cloud does not depend on which rank (or how many ranks) holds it."""
+    out = np.empty((len(ids), n_points, 3), dtype=np.float32)
+    for j, i in enumerate(ids):
+        b = int(i) % 64
+        key = (b, n_points, seed0)
+        if key not in _BASE_SHAPES:
+            _BASE_SHAPES[key] = synth_cloud(n_points, seed0 + b)
+        src = _BASE_SHAPES[key]
+        if i < 64:
+            out[j] = src
+        else:
+            rng = np.random.default_rng(10 ** 6 + int(i))
+            r = _random_rotation(rng).astype(np.float32)
+            out[j] = (src[rng.permutation(n_points)] @ r.T) * np.float32(rng.uniform(0.8, 1.2))
+    return out
+
+
 def synth_latents(n_rows, latentD=5, seed=0):
     g = torch.Generator().manual_seed(seed)
     return torch.randn(n_rows, latentD, generator=g, dtype=torch.float32)

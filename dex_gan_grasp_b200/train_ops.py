@@ -36,9 +36,10 @@ def _world():
     return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
 
 
-def _allreduce_sum(t):
+def _allreduce_sum(t, kind="bn_fwd"):
     if _world() > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        from . import dataparallel
+        dataparallel.all_reduce_sum(t, kind)
 
 
 def _check_cuda(x):
@@ -197,6 +198,8 @@ class _BatchNormFn(torch.autograd.Function):
             _native.check(L.dexgg_bn_apply(x.data_ptr(), _ld(x), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
                                            beta.data_ptr(), _native.ptr(res), _ld(res) if res is not None else 0,
                                            1 if act else 0, M, N, y.data_ptr(), N, st))
+        if running_mean is not None:  # written through raw pointers: tell torch (packed eval-mode weights key on the version)
+            torch.autograd.graph.increment_version([running_mean, running_var])
         ctx.act = bool(act)
         ctx.count = count
         ctx.has_res = residual is not None
@@ -224,7 +227,7 @@ class _BatchNormFn(torch.autograd.Function):
                 tot_g, tot_gx = sum_g, sum_gx
                 if _world() > 1:
                     both = torch.stack([sum_g, sum_gx])
-                    _allreduce_sum(both)
+                    _allreduce_sum(both, "bn_bwd")
                     tot_g, tot_gx = both[0].contiguous(), both[1].contiguous()
                 gx = torch.empty((M, N), dtype=torch.float32, device=dev)
                 _native.check(L.dexgg_bn_backward_apply(g.data_ptr(), _ld(g), x.data_ptr(), _ld(x), mean.data_ptr(),

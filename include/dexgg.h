@@ -130,10 +130,24 @@ int dexgg_discriminator_forward(const dexgg_net* net, const float* bps, int64_t 
  *   idx_out   [n_seg,k] i32 global row ids, -1 padded;  count_out [n_seg] i32 = min(#kept, k)
  *   best_out  [n_seg] f32 (may be NULL) best score of the segment — the caller raises the reference's ValueError
  *             when best < thresh (dexgangrasp.py:414-416);  score_out [n_seg,k] f32 (may be NULL).
- * k = rows_per_seg gives the reference's full sorted order.  rows_per_seg <= 16384.
+ * k = rows_per_seg gives the reference's full sorted order.
+ * dexgg_filter_topk: segments of at most 16384 rows (one CTA sorts a segment in shared memory).  dexgg_filter_topk_ws: any
+ * segment length (eval.py samples 5 x n_gt grasps per object, :317-322) — longer segments are sorted in the caller's
+ * workspace (dexgg_filter_topk_workspace_bytes, 0 for short segments).  Row ids are int32: M < 2^31.
+ * dexgg_filter_topk_gather: the batched pipeline's whole stage in ONE launch (segments <= 16384 rows): top-k as above plus the
+ * gather of the kept rows (the per-key torch.gather of dexgangrasp.py:421-435, without the tiled [k,4096] BPS block) into
+ *   packed_out [n_seg,k,14+n_joints] f32: score | global row id (int32 BITS) | rot 9 | transl 3 | joint_conf n_joints;
+ *   records beyond count hold id -1 and zeros.
  * ---------------------------------------------------------------------------------------------------------- */
 int dexgg_filter_topk(const float* p, int64_t M, int64_t rows_per_seg, float thresh, int k, int32_t* idx_out,
                       int32_t* count_out, float* best_out, float* score_out, void* stream);
+size_t dexgg_filter_topk_workspace_bytes(int64_t M, int64_t rows_per_seg);
+int dexgg_filter_topk_ws(const float* p, int64_t M, int64_t rows_per_seg, float thresh, int k, int32_t* idx_out,
+                         int32_t* count_out, float* best_out, float* score_out, void* workspace, size_t workspace_bytes,
+                         void* stream);
+int dexgg_filter_topk_gather(const float* p, int64_t M, int64_t rows_per_seg, float thresh, int k, const float* rot,
+                             const float* transl, const float* joint, int n_joints, int32_t* idx_out, int32_t* count_out,
+                             float* packed_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------
  * One fused linear layer, fp32 CUDA cores:  C = act(scale * (A·Wᵀ + bias) + shift + residual)  [+ C if accumulate].

@@ -60,7 +60,7 @@ def generator_forward(sd, z, bps, training=False, prefix="generator."):
 def normalize_vector(v):
     """utils.normalize_vector (utils.py:323-332) without its hard-coded `.cuda()` (utils.py:326)."""
     mag = torch.sqrt(v.pow(2).sum(1))
-    mag = torch.max(mag, torch.tensor([1e-8], dtype=v.dtype))
+    mag = torch.max(mag, torch.tensor([1e-8], dtype=v.dtype, device=v.device))
     return v / mag.view(-1, 1)
 
 
@@ -332,6 +332,49 @@ def evaluator_step(sd, opt, batch, dropout_masks=None, bce_weight=1.0, lr=1e-4, 
             sd[k].requires_grad_(False)
     adam_step(sd, dict(zip(keys, g)), opt, lr, beta1, 0.999, 1e-8, wd)
     return {"total_loss_eva": loss.item(), "bce_loss": loss.item()}, dict(zip(keys, g))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# evaluation helpers (dexgangrasp.py:309-365)
+# ---------------------------------------------------------------------------------------------------------
+def eval_evaluator_loss(sd, batch, bce_weight=1.0):
+    """eval_dexevaluator_loss (dexgangrasp.py:325-332): eval-mode forward, BCE against the labels (:142-147)."""
+    with torch.no_grad():
+        p = evaluator_forward(sd, batch["bps_object"].float(), batch["rot_matrix"].float(), batch["transl"].float(), training=False)
+        loss = bce_weight * F.binary_cross_entropy(p, batch["label"].float().unsqueeze(-1))
+    return {"total_loss_eva": loss.item(), "bce_loss": loss.item()}, p
+
+
+def eval_evaluator_accuracy(sd, batch, logit_thresh=0.5):
+    """eval_dexevaluator_accuracy (dexgangrasp.py:309-322) after eval(): scores thresholded at 0.5 (utils.py:60-64), then
+    losses.accuracy_evaluator (losses.py:5-16): TP / P, TN / N.  Returns (pos_acc, neg_acc, pred [B,1], gt [B,1], scores)."""
+    with torch.no_grad():
+        p = evaluator_forward(sd, batch["bps_object"].float(), batch["rot_matrix"].float(), batch["transl"].float(), training=False)
+    pred = (p >= logit_thresh).float()
+    gt = batch["label"].float().unsqueeze(-1)
+    correct = torch.eq(pred, gt)
+    pos = torch.sum(correct * gt) / torch.sum(gt)
+    neg = torch.sum(correct * (1.0 - gt)) / torch.sum(1.0 - gt)
+    return pos.item(), neg.item(), pred.numpy(), gt.numpy(), p.numpy()
+
+
+def eval_generator_loss(sd, batch, z, bce_weight=1.0):
+    """eval_dexgangrasp_generator_loss (dexgangrasp.py:334-365), non-WGAN: eval-mode G and D, the generator loss terms of
+    compute_loss_dexgangrasp_generator (:272-307) under no_grad."""
+    bps = batch["bps_object"].float()
+    rot = batch["rot_matrix"].float()
+    transl = batch["transl"].float()
+    joint = batch["joint_conf"].float()
+    with torch.no_grad():
+        fake = generator_forward(sd, z, bps, training=False)
+        fake_rot = rot_matrix_from_ortho6d(fake["rot_6D"])
+        score = discriminator_forward(sd, bps, fake_rot, fake["transl"], fake["joint_conf"], training=False)
+        l_fake = bce_weight * bce(score, 1.0)
+        l_t = 100.0 * F.mse_loss(fake["transl"], transl)
+        l_r = 1.0 * F.mse_loss(fake_rot.reshape(-1, 9), rot.reshape(-1, 9))
+        l_j = 10.0 * F.mse_loss(fake["joint_conf"], joint)
+    return {"gen_loss_fake": l_fake.item(), "transl_loss": l_t.item(), "rot_loss": l_r.item(), "conf_loss": l_j.item(),
+            "total_loss_gen": (l_fake + (l_t + l_r + l_j)).item()}
 
 
 def refine_grasps_gradient(sd_eva, data, num_refine_steps=10):

@@ -1,6 +1,7 @@
 """Turns the ncu artefacts in gpurun_out/ into the tracked summaries under profiles/.
   python tools/ncu_summary.py launches gpurun_out/r01_launches_fp32.csv profiles/r01_launches_fp32.md
   python tools/ncu_summary.py full gpurun_out/r01_bps.ncu-rep profiles/r01_bps_ncu_full.md
+  python tools/ncu_summary.py traffic gpurun_out/r02_chain.ncu-rep profiles/ncu_traffic.json   (merged into the JSON bench.py reads)
 """
 import collections
 import csv
@@ -53,5 +54,39 @@ def full(src, dst):
             f.write("\n")
 
 
+def traffic(src, dst):
+    """Per-kernel DRAM traffic / duration / pipe activity of one `ncu --set full` capture, merged into the JSON that
+    bench.py's `roofline.traffic` reads (so the number in the bench line is reproducible from a tracked file)."""
+    import json
+    import os
+    out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    db = json.load(open(dst)) if os.path.exists(dst) else {}
+
+    def val(r, key, want_unit=None):
+        i = hdr.index(key)
+        v = float(r[i].replace(",", ""))
+        u = units[i].lower()
+        if want_unit == "mb":
+            v *= {"byte": 1e-6, "kbyte": 1e-3, "mbyte": 1.0, "gbyte": 1e3}[u]
+        if want_unit == "ms":
+            v *= {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "nsecond": 1e-6, "second": 1e3, "s": 1e3}[u]
+        return v
+    for r in rows[2:]:
+        name = r[hdr.index("Kernel Name")].split("(")[0].replace("void ", "").strip()
+        rec = {"dram_read_mb": val(r, "dram__bytes_read.sum", "mb"), "dram_write_mb": val(r, "dram__bytes_write.sum", "mb"),
+               "time_ms": val(r, "gpu__time_duration.sum", "ms"), "grid": r[hdr.index("launch__grid_size")], "source": os.path.basename(src)}
+        for k, short in (("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "tensor_active_pct"),
+                         ("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "fma_active_pct"),
+                         ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue_active_pct"),
+                         ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps_active_pct")):
+            if k in hdr:
+                rec[short] = val(r, k)
+        rec["dram_total_mb"] = rec["dram_read_mb"] + rec["dram_write_mb"]
+        db[name] = rec
+    json.dump(db, open(dst, "w"), indent=1, sort_keys=True)
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](sys.argv[2], sys.argv[3])
