@@ -42,6 +42,7 @@ SIGNATURES = {
                                  c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "dexgg_linear_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_int64, c_int, c_void_p, c_void_p, c_int64, c_void_p]),
+    "dexgg_gemm_bf16": (c_int, [c_void_p, c_void_p]),
     "dexgg_f32_to_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_f32_to_bf16_t": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_rot6d_forward": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
@@ -66,6 +67,17 @@ SIGNATURES = {
     "dexgg_adam_step_dev": (c_int, [c_void_p, c_int, c_float, c_float, c_float, c_float, c_float, c_void_p, c_void_p]),
     "dexgg_fp32_pipe_probe": (c_int, [c_int, c_int, ctypes.POINTER(c_float), ctypes.POINTER(ctypes.c_double)]),
 }
+
+
+class GemmSeg(ctypes.Structure):
+    _fields_ = [("A", c_void_p), ("lda", c_int64), ("a_mn_major", c_int), ("B", c_void_p), ("ldb", c_int64), ("b_mn_major", c_int),
+                ("K", c_int)]
+
+
+class Gemm(ctypes.Structure):
+    """include/dexgg.h: dexgg_gemm"""
+    _fields_ = [("M", c_int), ("N", c_int), ("n_seg", c_int), ("seg", GemmSeg * 3), ("bias", c_void_p), ("act_from", c_int),
+                ("C16", c_void_p), ("C32", c_void_p), ("ldc", c_int64), ("accumulate", c_int), ("split_k", c_int), ("tile_n", c_int)]
 
 
 class DexggError(RuntimeError):

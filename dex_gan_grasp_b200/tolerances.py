@@ -17,7 +17,7 @@ BF16_POSE_TOL = 2e-2
 # the evaluator's own drift.  This single epsilon also defines the filtered-set contract: per object, every row whose ORACLE
 # score is more than EPS above the cut (max(thresh, k-th best oracle score)) must be kept, no row more than EPS below it may
 # be; rows within EPS of the cut may fall either way.
-BF16_PIPELINE_EPS = 2.5e-2
+BF16_PIPELINE_EPS = 1e-2
 
 # bf16 tensor-core TRAINING step (C5) against the fp32 oracle step from identical state: losses relative, gradients in the
 # relative L2 norm per tensor / per tensor of < 64 elements (head biases: sums of cancelling per-sample terms) / over all

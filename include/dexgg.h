@@ -167,6 +167,42 @@ int dexgg_linear_f32(const float* A, int64_t lda, int trans_a, const float* W, i
 int dexgg_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, const float* bias,
                       const float* scale, const float* shift, const void* residual_bf16, int64_t ldr, int act, void* C_bf16,
                       float* C_f32, int64_t ldc, void* stream);
+/* ------------------------------------------------------------------------------------------------------------
+ * General bf16 tensor-core GEMM of the training step (csrc/gemm_umma.cu):
+ *     C[M,N] = act(sum_s op(A_s)[M,K_s] . op(B_s)[N,K_s]^T + bias)
+ * Up to three K segments accumulate into one TMEM tile (the reference's torch.cat of ResBlock inputs, networks.py:97,153,325,
+ * is never materialised).  Operand layouts, bf16, row pitch (ld, elements) a multiple of 8:
+ *     K-major   element (i, k) at p[i*ld + k]    (forward: activations [rows,K], nn.Linear weights [N_out,K_in])
+ *     MN-major  element (i, k) at p[k*ld + i]    (dgrad reads W [N_out,K_in] as the [K_in x N_out] operand; wgrad reads
+ *                                                 dY [rows,N_out] and X [rows,K_in] as they lie: no transposed copies)
+ * Replaces the cuBLAS calls behind nn.Linear forward / backward in DexGanGrasp.update_dexgangrasp / update_dexevaluator
+ * (models/dexgangrasp.py:739-823).  act_from: columns >= act_from get LeakyReLU(0.2) (>= N: none).  split_k > 1 splits the
+ * contraction over CTAs and accumulates raw fp32 partial sums into C32 with atomic adds (C32 zeroed by the caller; no bias /
+ * act / bf16 output): for outputs of few tiles and a long contraction (weight gradients of the small layers).
+ * ---------------------------------------------------------------------------------------------------------- */
+typedef struct {
+    const void* A;      /* bf16 */
+    int64_t lda;
+    int a_mn_major;
+    const void* B;      /* bf16 */
+    int64_t ldb;
+    int b_mn_major;
+    int K;
+} dexgg_gemm_seg;
+typedef struct {
+    int M, N, n_seg;
+    dexgg_gemm_seg seg[3];
+    const float* bias;  /* [N] or NULL */
+    int act_from;
+    void* C16;          /* bf16 [M, ldc] or NULL */
+    float* C32;         /* f32  [M, ldc] or NULL */
+    int64_t ldc;
+    int accumulate;     /* 1: C32 += result (split_k == 1) */
+    int split_k;        /* 0 / 1: no split */
+    int tile_n;         /* 0: chosen by the library; else 64 / 128 / 192 / 256 */
+} dexgg_gemm;
+int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream);
+
 int dexgg_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream);
 int dexgg_f32_to_bf16_t(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream);
 
