@@ -2,16 +2,9 @@
 // Reference: utils.rot_matrix_from_ortho6d / normalize_vector / cross_product (DexGanGrasp/utils/utils.py:380-394,323-332,68-78).
 //   x = a / max(|a|,1e-8);  z = (x × b) / max(|x × b|,1e-8);  y = z × x;  R = [x y z] as columns (row-major [M,3,3]).
 #include "common.cuh"
+#include "pose.cuh"
 
 namespace dexgg {
-
-struct V3 {
-    float x, y, z;
-};
-__device__ __forceinline__ V3 cross(V3 p, V3 q) { return {p.y * q.z - p.z * q.y, p.z * q.x - p.x * q.z, p.x * q.y - p.y * q.x}; }
-__device__ __forceinline__ float dot(V3 p, V3 q) { return p.x * q.x + p.y * q.y + p.z * q.z; }
-__device__ __forceinline__ V3 add(V3 p, V3 q) { return {p.x + q.x, p.y + q.y, p.z + q.z}; }
-__device__ __forceinline__ V3 scale(V3 p, float s) { return {p.x * s, p.y * s, p.z * s}; }
 
 __global__ void rot6d_forward_kernel(const float* __restrict__ r6, int64_t M, float* __restrict__ rot) {
     const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -37,6 +37,11 @@ def allreduce_gradients(module):
     """Average the gradients of `module` over all ranks with a single flat allreduce."""
     if not is_parallel():
         return
+    flat = getattr(module, "_dexgg_flat_grad", None)
+    if flat is not None:  # train_engine: every .grad is a view of one flat buffer -> exchange it in place (no cat, no copy-back)
+        all_reduce_sum(flat, "grad")
+        flat.div_(dist.get_world_size())
+        return
     params = [p for p in module.parameters() if p.grad is not None]
     if not params:
         return

@@ -442,7 +442,28 @@ class DexGanGrasp(object):
         from . import train_ops
         train_ops.set_precision(self.cfg.get("precision", "fp32"))
 
+    def train_engine_name(self):
+        return ("hand-scheduled fused step (train_engine.py: gemm_umma.cu + train_fused.cu)" if self._use_engine()
+                else "autograd Functions over the dexgg kernels (train_ops.py)")
+
+    def _use_engine(self):
+        """The fused bf16 step (train_engine.py) runs the BCE variant on one rank; the WGAN-GP variant, the fp32 parity mode and
+        cfg['train_engine'] = False use the autograd-Function path of train_ops.py."""
+        from . import dataparallel
+        return (self.cfg.get("precision", "fp32") == "bf16" and not self.is_wgan and self.cfg.get("train_engine", True)
+                and not dataparallel.is_parallel())
+
+    def _engine(self, rows):
+        from .train_engine import TrainEngine
+        eng = getattr(self, "_train_engine", None)
+        if eng is None or eng.B != rows:
+            eng = self._train_engine = TrainEngine(self, rows)
+        return eng
+
     def update_dexevaluator(self, data):
+        if self._use_engine():
+            self.DexEvaluator.train()
+            return self._engine(int(data["bps_object"].shape[0])).evaluator_step(data)
         self._train_precision()
         self.DexEvaluator.train()
         out = self.DexEvaluator(data)
@@ -463,12 +484,17 @@ class DexGanGrasp(object):
         latent batch and the three WGAN-GP interpolation weights."""
         is_wgan = self.is_wgan
         gen_loss = self.compute_loss_dexgangrasp_generator_wass if is_wgan else self.compute_loss_dexgangrasp_generator
-        self._train_precision()
         self.DexGANGrasp.train()
         G, D = self.DexGANGrasp.generator, self.DexGANGrasp.discriminator
         n_samples = real_data["bps_object"].shape[0]
         if Zgen is None:
             Zgen = torch.randn((n_samples, self.DexGANGrasp.latentD), dtype=self.DexGANGrasp.dtype, device=self.DexGANGrasp.device)
+        if self._use_engine():
+            out = self._engine(int(n_samples)).gan_step(real_data, is_train_gen, Zgen.to(self.device))
+            if is_train_gen:
+                real_data["rot_matrix"] = real_data["rot_matrix"].view(n_samples, -1)  # the reference's side effect (:810)
+            return out
+        self._train_precision()
         y_fake = G(Zgen, real_data["bps_object"].to(self.DexGANGrasp.device))
         fake_rot_6D, fake_transl, fake_joint_conf = y_fake["rot_6D"], y_fake["transl"], y_fake["joint_conf"]
         y_fake["rot_matrix"] = utils.rot_matrix_from_ortho6d(y_fake["rot_6D"])

@@ -1,0 +1,523 @@
+"""The bf16 training step of DexGanGrasp.update_dexgangrasp / update_dexevaluator (DexGanGrasp/models/dexgangrasp.py:739-823)
+as a hand-scheduled sequence of fused sm_100a kernels (csrc/gemm_umma.cu, csrc/train_fused.cu) - no autograd graph, no
+torch.cat, no dtype-conversion passes, ~130 launches per GAN + evaluator step (the autograd-Function path of train_ops.py
+needs ~600), capturable as one CUDA graph (graph_step.CapturedTrainStep).
+
+What makes the schedule short:
+  * every network's input BatchNorm sees the same BPS batch: its statistics and xhat = (bps - mean) / std are computed ONCE
+    per step; each network's gamma / beta are folded into its first-layer weights when they are converted to bf16
+    (dexgg_prep_weights), and dexgg_unfold_grads maps the gradients of the folded weights back to fc1 / fc3 .weight and to the
+    input BatchNorm's own gamma / beta - so no GEMM computes a gradient wrt the 4096 BPS columns;
+  * torch.cat([X0, X]) (networks.py:97,153,325) is a second K segment of the GEMM;
+  * fc1 and fc3 of a ResBlock are one N = 768 GEMM whose epilogue applies LeakyReLU to the fc3 columns;
+  * a train-mode BatchNorm (+ skip, LeakyReLU, dropout) is one column-slab kernel forward and one backward;
+  * dgrad / wgrad read weights and activations in their natural layouts (MN-major tcgen05 operands): no transposes;
+  * the discriminator's real and fake batches of the D step run as ONE double batch with per-half statistics.
+Parameters stay fp32 nn.Parameters (master weights); their .grad tensors are views of one flat buffer per network, filled by
+the kernels; the optimizers are the reference's (train_ops.DexggAdam = torch.optim.Adam state + one fused launch).
+"""
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from . import _native
+from ._native import BnBwd, BnFwd, FirstLayer, Gemm, PlainJob, RunEntry, ScoreHead, TailSrc, WeightJobs
+
+BPS, HID, INNER, NCAT = 4096, 512, 256, 768
+TAILW = 64          # the tail columns are stored 64 wide (zero padded): 128-byte rows for TMA, N tiles of 64 for the dgrad
+LDXT = HID + TAILW  # [X (512) | tail (64)]
+EPS = 1e-5
+
+
+def _L():
+    return _native.lib()
+
+
+def _st(dev):
+    return _native.stream_ptr(dev)
+
+
+def _world():
+    return dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+
+
+class _Block:
+    """Static description + device buffers of one ResBlock inside a network."""
+
+    def __init__(self, rb, cmap, dmap, has_x, dev):
+        self.rb, self.has_x = rb, has_x
+        self.Fin = rb.fc1.weight.shape[1]
+        self.cmap = torch.tensor(cmap, dtype=torch.int32, device=dev)
+        self.dmap = torch.tensor(dmap, dtype=torch.int32, device=dev)
+        self.ldxt = LDXT if has_x else TAILW
+        self.Wb = torch.zeros((NCAT, BPS), dtype=torch.bfloat16, device=dev)
+        self.Wxt = torch.zeros((NCAT, self.ldxt), dtype=torch.bfloat16, device=dev)
+        self.W2 = torch.zeros((HID, INNER), dtype=torch.bfloat16, device=dev)
+        self.bias13 = torch.zeros((NCAT,), dtype=torch.float32, device=dev)
+        self.dWb = torch.zeros((NCAT, BPS), dtype=torch.float32, device=dev)
+        self.dWxt = torch.zeros((NCAT, self.ldxt), dtype=torch.float32, device=dev)
+
+
+class _Net:
+    """One network (generator / discriminator / evaluator): blocks, input BatchNorm, bf16 operand buffers, activations."""
+
+    def __init__(self, kind, module, in_bn, blocks, n_tail, tail_bn, head, rows, groups, dev, optimizer):
+        self.kind, self.module, self.in_bn, self.n_tail, self.tail_bn, self.head = kind, module, in_bn, n_tail, tail_bn, head
+        self.rows, self.groups, self.dev, self.optimizer = rows, groups, dev, optimizer
+        self.blocks = blocks
+        nb = len(blocks)
+        R = rows
+        bf = dict(dtype=torch.bfloat16, device=dev)
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.tail1 = torch.zeros((R, TAILW), **bf)
+        self.XT = [None] + [torch.zeros((R, LDXT), **bf) for _ in range(nb - 1)]  # input of block b >= 1: [X_{b-1} | tail]
+        self.Xlast = torch.zeros((R, HID), **bf)
+        self.T = [torch.zeros((R, NCAT), **bf) for _ in range(nb)]
+        self.H = [torch.zeros((R, INNER), **bf) for _ in range(nb)]
+        self.Y = [torch.zeros((R, HID), **bf) for _ in range(nb)]
+        self.stat1 = [torch.zeros((2, groups, INNER), **f32) for _ in range(nb)]  # [mean | invstd]
+        self.stat2 = [torch.zeros((2, groups, HID), **f32) for _ in range(nb)]
+        self.GY = torch.zeros((R, HID), **bf)
+        self.GH = torch.zeros((R, INNER), **bf)
+        self.G13 = torch.zeros((R, NCAT), **bf)
+        self.gXT = [torch.zeros((R, TAILW), **bf)] + [torch.zeros((R, LDXT), **bf) for _ in range(nb - 1)]
+        self.tail_stat = torch.zeros((groups, 2, TAILW), **f32)  # per group: mean | invstd of the tail columns
+        self.db13 = torch.zeros((nb, NCAT), **f32)  # column sums of the first-layer output gradient (fc3 part), zeroed per backward
+        self.dl = torch.zeros((R,), **f32)
+        self.p = torch.zeros((R,), **f32)
+        # flat gradient buffer; every parameter's .grad is a view into it (one memset to zero, one allreduce to exchange)
+        self.params = [p for p in module.parameters()]
+        self.flat_grad = torch.zeros((sum(p.numel() for p in self.params),), **f32)
+        module._dexgg_flat_grad = self.flat_grad  # dataparallel.allreduce_gradients exchanges this buffer in place
+        self.attach()
+
+    def attach(self):
+        """(Re-)point every parameter's .grad at its slice of the flat buffer (someone may have set it to None)."""
+        off = 0
+        for p in self.params:
+            n = p.numel()
+            if p.grad is None or p.grad.data_ptr() != self.flat_grad.data_ptr() + 4 * off:
+                p.grad = self.flat_grad[off:off + n].view_as(p)
+            off += n
+
+
+def _maps(kind, b, n_tail, Fin):
+    """cmap / dmap of block b's input columns in the reference's torch.cat order (networks.py:92-97, 150-153, 318-325)."""
+    cmap, dmap = [-1] * Fin, [0] * Fin
+    xo = BPS + (HID if b > 0 else 0)  # first tail column inside [bps 4096 | X 512 | tail]
+    for c in range(Fin):
+        if kind == "G":      # [z | bps] , [z | bps | X]
+            if c < n_tail:
+                dmap[c] = xo + c
+            elif c < n_tail + BPS:
+                cmap[c], dmap[c] = c - n_tail, c - n_tail
+            else:
+                dmap[c] = BPS + (c - n_tail - BPS)
+        elif kind == "D":    # [bps | pose] , [bps | pose | X]
+            if c < BPS:
+                cmap[c], dmap[c] = c, c
+            elif c < BPS + n_tail:
+                cmap[c], dmap[c] = c, xo + (c - BPS)
+            else:
+                dmap[c] = BPS + (c - BPS - n_tail)
+        else:                # E: [bps | pose] , [X | bps | pose]
+            x = HID if b > 0 else 0
+            if c < x:
+                dmap[c] = BPS + c
+            elif c < x + BPS:
+                cmap[c], dmap[c] = c - x, c - x
+            else:
+                cmap[c], dmap[c] = BPS + (c - x - BPS), xo + (c - x - BPS)
+    return cmap, dmap
+
+
+class TrainEngine:
+    def __init__(self, model, batch_rows):
+        """model: dexgangrasp.DexGanGrasp wrapper in training mode; batch_rows: rows per rank."""
+        self.model = model
+        dev = model.device
+        self.dev = dev
+        B = int(batch_rows)
+        self.B = B
+        G, D, E = model.DexGANGrasp.generator, model.DexGANGrasp.discriminator, model.DexEvaluator
+        self.nJ = G.gen_joint_conf.out_features
+        self.zD = G.latentD
+        nt_pose = 12 + self.nJ
+
+        def blocks(kind, rbs, n_tail):
+            return [_Block(rb, *_maps(kind, b, n_tail, rb.fc1.weight.shape[1]), b > 0, dev) for b, rb in enumerate(rbs)]
+        self.G = _Net("G", G, G.gen_bn1, blocks("G", [G.gen_rb1, G.gen_rb2], self.zD), self.zD, False, None, B, 1, dev,
+                      model.optim_dexgangrasp_generator)
+        self.D = _Net("D", D, D.disc_bn1, blocks("D", [D.disc_rb1, D.disc_rb2], nt_pose), nt_pose, True, D.out_success, 2 * B, 2, dev,
+                      model.optim_dexgangrasp_discriminator)
+        self.E = _Net("E", E, E.bn1, blocks("E", [E.rb1, E.rb2, E.rb3], 12), 12, True, E.out_success, B, 1, dev, model.optim_dexevaluator)
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.bps_stat = torch.zeros((3, BPS), **f32)  # mean | var | invstd of the step's BPS batch
+        self.xhat = torch.zeros((2 * B, BPS), dtype=torch.bfloat16, device=dev)
+        # generator heads: rows (joint nJ | rot6d 6 | transl 3) padded to 32
+        self.Wh = torch.zeros((32, HID), dtype=torch.bfloat16, device=dev)
+        self.bh = torch.zeros((32,), **f32)
+        self.OUT = torch.zeros((B, 32), **f32)
+        self.gHeads = torch.zeros((B, 32), dtype=torch.bfloat16, device=dev)
+        self.dWh = torch.zeros((32, HID), **f32)
+        self.dbh = torch.zeros((32,), **f32)
+        self.gX = torch.zeros((B, HID), dtype=torch.bfloat16, device=dev)
+        self.fake_rot = torch.zeros((B, 9), **f32)
+        self.fake_transl = torch.zeros((B, 3), **f32)
+        self.fake_joint = torch.zeros((B, self.nJ), **f32)
+        self.gPose = torch.zeros((B, nt_pose), **f32)
+        self.loss = torch.zeros((16,), **f32)  # 0 bce_real 1 bce_fake 2 gen_fake 3 transl 4 rot 5 conf 6 eva
+        self.seed = torch.zeros((1,), dtype=torch.int64, device=dev)  # dropout seed, bumped on the device every evaluator step
+        self.seed.fill_(0x1234567)
+        mix = torch.zeros((10, 16), **f32)
+        bw = float(model.bce_weight)
+        mix[0, 0] = mix[0, 1] = 0.5   # total_loss_disc = (real + fake) / 2
+        mix[1, 0] = 1.0               # bce_loss_real
+        mix[2, 1] = 1.0               # bce_loss_fake
+        mix[3, 2] = 1.0               # gen_loss_fake
+        mix[4, 3] = 1.0               # transl_loss (coefficient applied in the kernel)
+        mix[5, 4] = 1.0               # rot_loss
+        mix[6, 5] = 1.0               # conf_loss
+        mix[7, 2] = mix[7, 3] = mix[7, 4] = mix[7, 5] = 1.0  # total_loss_gen
+        mix[8, 6] = 1.0               # total_loss_eva
+        self.mix, self.bw = mix, bw
+
+    # ------------------------------------------------------------------------------------------------ kernel wrappers
+    def _gemm(self, M, N, segs, bias=None, act_from=None, C16=None, C32=None, ldc=None, split_k=0, accumulate=0):
+        g = Gemm()
+        g.M, g.N, g.n_seg = int(M), int(N), len(segs)
+        for i, (A, lda, a_mn, Bm, ldb, b_mn, K) in enumerate(segs):
+            s = g.seg[i]
+            s.A, s.lda, s.a_mn_major, s.B, s.ldb, s.b_mn_major, s.K = A, int(lda), int(a_mn), Bm, int(ldb), int(b_mn), int(K)
+        g.bias = bias.data_ptr() if bias is not None else None
+        g.act_from = int(N if act_from is None else act_from)
+        g.C16 = C16.data_ptr() if C16 is not None else None
+        g.C32 = C32.data_ptr() if C32 is not None else None
+        g.ldc, g.accumulate, g.split_k, g.tile_n = int(ldc), int(accumulate), int(split_k), 0
+        _native.check(_L().dexgg_gemm_bf16(ctypes.byref(g), _st(self.dev)))
+
+    def _bn_fwd(self, x, ldx, C, rpg, groups, bn, stat, y, ldy, res=None, ldr=0, drop=None):
+        a = BnFwd()
+        a.x, a.ldx, a.C, a.rows_per_group, a.n_groups = x, ldx, C, rpg, groups
+        a.gamma, a.beta = bn.weight.data_ptr(), bn.bias.data_ptr()
+        a.mean, a.invstd = stat[0].data_ptr(), stat[1].data_ptr()
+        a.eps, a.count_total = EPS, float(rpg)
+        a.residual, a.ldr, a.act = res, ldr, 1
+        if drop is not None:
+            mask, p, stream = drop
+            if mask is not None:
+                a.drop_mask, a.ldm = mask.data_ptr(), mask.stride(0)
+            a.drop_p, a.drop_seed, a.drop_stream = float(p), self.seed.data_ptr(), int(stream)
+        a.y, a.ldy, a.mode = y, ldy, 0
+        _native.check(_L().dexgg_bn_fwd_slab(ctypes.byref(a), _st(self.dev)))
+
+    def _bn_bwd(self, C, rpg, groups, bn, stat, x, ldx, out, ldo, gx, ldgx, g=None, ldg=0, rank1=None, skip=None, lds=0, gskip=None, ldgs=0,
+                dbias_skip=None, want_wgrad=True, drop=None):
+        a = BnBwd()
+        if g is not None:
+            a.g, a.ldg = g, ldg
+        else:
+            dl, w, dw_out = rank1
+            a.dl, a.w, a.dw_out = dl.data_ptr(), w.data_ptr(), (dw_out.data_ptr() if (dw_out is not None and want_wgrad) else None)
+        a.out, a.ldo, a.act = out, ldo, 1
+        if drop is not None:
+            mask, p, stream = drop
+            if mask is not None:
+                a.drop_mask, a.ldm = mask.data_ptr(), mask.stride(0)
+            a.drop_p, a.drop_seed, a.drop_stream = float(p), self.seed.data_ptr(), int(stream)
+        a.x, a.ldx = x, ldx
+        a.mean, a.invstd, a.gamma = stat[0].data_ptr(), stat[1].data_ptr(), bn.weight.data_ptr()
+        a.C, a.rows_per_group, a.n_groups, a.count_total = C, rpg, groups, float(rpg)
+        if want_wgrad:
+            a.dgamma, a.dbeta = bn.weight.grad.data_ptr(), bn.bias.grad.data_ptr()
+        a.gx, a.ldgx = gx, ldgx
+        if skip is not None:
+            a.skip, a.lds, a.gskip, a.ldgs = skip, lds, gskip, ldgs
+            a.dbias_skip = dbias_skip if want_wgrad else None
+        a.mode = 0
+        _native.check(_L().dexgg_bn_bwd_slab(ctypes.byref(a), _st(self.dev)))
+
+    @staticmethod
+    def _tail_src(tensors):
+        s = TailSrc()
+        f64 = tensors[0].dtype == torch.float64
+        for i in range(3):
+            if i < len(tensors):
+                t = tensors[i]
+                assert t.is_contiguous() and (t.dtype == torch.float64) == f64 and t.dtype in (torch.float32, torch.float64)
+                s.p[i], s.n[i] = t.data_ptr(), t.numel() // t.shape[0]
+            else:
+                s.p[i], s.n[i] = None, 0
+        s.f64 = int(f64)
+        return s
+
+    def _tail_pack(self, net, tensors, row0, rows, group):
+        """Normalise (train-mode BatchNorm statistics of this group) and write the tail columns of rows [row0, row0 + rows)."""
+        src = self._tail_src(tensors)
+        dsts = [net.tail1] + list(net.XT[1:])  # tail-only input of block 0, then the [X | tail] inputs of the later blocks
+        P, LD, C0 = (ctypes.c_void_p * 3)(), (ctypes.c_int64 * 3)(), (ctypes.c_int * 3)()
+        for i in range(3):
+            if i < len(dsts):
+                P[i], LD[i], C0[i] = dsts[i][row0:].data_ptr(), dsts[i].stride(0), (0 if i == 0 else HID)
+            else:
+                P[i], LD[i], C0[i] = None, 0, 0
+        st = net.tail_stat[group]
+        rm = rv = None
+        if net.tail_bn:
+            rm = net.in_bn.running_mean.data_ptr() + 4 * BPS
+            rv = net.in_bn.running_var.data_ptr() + 4 * BPS
+        _native.check(_L().dexgg_tail_pack(ctypes.byref(src), rows, int(net.tail_bn), EPS, float(rows), float(net.in_bn.momentum or 0.1),
+                                           st[0].data_ptr(), st[1].data_ptr(), rm, rv, P, LD, C0, 0, None, _st(self.dev)))
+
+    # ------------------------------------------------------------------------------------------------ weights
+    def _weight_jobs(self, net, grads):
+        J = WeightJobs()
+        J.n_first = len(net.blocks)
+        for i, blk in enumerate(net.blocks):
+            rb, F = blk.rb, J.first[i]
+            F.W1, F.W3, F.b1, F.b3 = rb.fc1.weight.data_ptr(), rb.fc3.weight.data_ptr(), rb.fc1.bias.data_ptr(), rb.fc3.bias.data_ptr()
+            F.Fin, F.cmap, F.dmap = blk.Fin, blk.cmap.data_ptr(), blk.dmap.data_ptr()
+            F.in_gamma, F.in_beta = net.in_bn.weight.data_ptr(), net.in_bn.bias.data_ptr()
+            F.Wb, F.Wxt, F.ldxt, F.bias13 = blk.Wb.data_ptr(), blk.Wxt.data_ptr(), blk.ldxt, blk.bias13.data_ptr()
+            if grads:
+                F.dWb, F.dWxt, F.db13 = blk.dWb.data_ptr(), blk.dWxt.data_ptr(), net.db13[i].data_ptr()
+                F.gW1, F.gW3 = rb.fc1.weight.grad.data_ptr(), rb.fc3.weight.grad.data_ptr()
+                F.gb1, F.gb3 = rb.fc1.bias.grad.data_ptr(), rb.fc3.bias.grad.data_ptr()
+                F.g_in_gamma, F.g_in_beta = net.in_bn.weight.grad.data_ptr(), net.in_bn.bias.grad.data_ptr()
+        n = 0
+        if not grads:
+            for blk in net.blocks:  # fc2 weights: plain bf16 copies
+                P = J.plain[n]
+                P.src, P.lds, P.rows, P.cols, P.dst, P.ldd = blk.rb.fc2.weight.data_ptr(), INNER, HID, INNER, blk.W2.data_ptr(), INNER
+                n += 1
+        if net.kind == "G":
+            G = net.module
+            r = 0
+            for lin, rows in ((G.gen_joint_conf, self.nJ), (G.gen_rot, 6), (G.gen_transl, 3)):
+                P = J.plain[n]
+                if grads:
+                    P.gsrc, P.ldgs, P.rows, P.cols, P.gdst, P.ldgd = self.dWh[r:].data_ptr(), HID, rows, HID, lin.weight.grad.data_ptr(), HID
+                else:
+                    P.src, P.lds, P.rows, P.cols, P.dst, P.ldd = lin.weight.data_ptr(), HID, rows, HID, self.Wh[r:].data_ptr(), HID
+                n += 1
+                r += rows
+        J.n_plain = n
+        return J
+
+    def prep(self, net):
+        _native.check(_L().dexgg_prep_weights(ctypes.byref(self._weight_jobs(net, False)), _st(self.dev)))
+        if net.kind == "G":
+            G = net.module
+            torch.cat([G.gen_joint_conf.bias.detach(), G.gen_rot.bias.detach(), G.gen_transl.bias.detach()], out=self.bh[:self.nJ + 9])
+
+    def unfold(self, net):
+        _native.check(_L().dexgg_unfold_grads(ctypes.byref(self._weight_jobs(net, True)), _st(self.dev)))
+        if net.kind == "G":
+            G = net.module
+            nJ = self.nJ
+            G.gen_joint_conf.bias.grad.copy_(self.dbh[:nJ])
+            G.gen_rot.bias.grad.copy_(self.dbh[nJ:nJ + 6])
+            G.gen_transl.bias.grad.copy_(self.dbh[nJ + 6:nJ + 9])
+
+    # ------------------------------------------------------------------------------------------------ forward / backward of a block stack
+    def _block_in(self, net, b):
+        return (net.tail1, TAILW, net.n_tail) if b == 0 else (net.XT[b], LDXT, HID + net.n_tail)
+
+    def forward_blocks(self, net, R, groups, xhat, drops=None):
+        rpg = R // groups
+        nb = len(net.blocks)
+        for b, blk in enumerate(net.blocks):
+            rb = blk.rb
+            xin, ldx, K2 = self._block_in(net, b)
+            self._gemm(R, NCAT, [(xhat.data_ptr(), BPS, 0, blk.Wb.data_ptr(), BPS, 0, BPS), (xin.data_ptr(), ldx, 0, blk.Wxt.data_ptr(), blk.ldxt, 0, K2)],
+                       bias=blk.bias13, act_from=INNER, C16=net.T[b], ldc=NCAT)
+            self._bn_fwd(net.T[b].data_ptr(), NCAT, INNER, rpg, groups, rb.bn1, net.stat1[b], net.H[b].data_ptr(), INNER)
+            self._gemm(R, HID, [(net.H[b].data_ptr(), INNER, 0, blk.W2.data_ptr(), INNER, 0, INNER)], bias=rb.fc2.bias, C16=net.Y[b], ldc=HID)
+            out, ldo = (net.XT[b + 1], LDXT) if b + 1 < nb else (net.Xlast, HID)
+            self._bn_fwd(net.Y[b].data_ptr(), HID, HID, rpg, groups, rb.bn2, net.stat2[b], out.data_ptr(), ldo,
+                         res=net.T[b][:, INNER:].data_ptr(), ldr=NCAT, drop=(drops[b] if drops else None))
+
+    def running_update(self, net, groups, rpg):
+        """BatchNorm buffer updates of one pass: hidden layers from the saved statistics, the input BatchNorm's BPS columns from
+        the step's shared statistics (its tail columns were updated by dexgg_tail_pack); num_batches_tracked += groups."""
+        ents = (RunEntry * 24)()
+        n = 0
+
+        def put(bn, mean, second, C, is_var, same_row, nbt=True):
+            nonlocal n
+            e = ents[n]
+            e.running_mean, e.running_var, e.mean, e.second = bn.running_mean.data_ptr(), bn.running_var.data_ptr(), mean, second
+            e.num_batches_tracked = bn.num_batches_tracked.data_ptr() if nbt else None
+            e.C, e.n_groups, e.second_is_var, e.same_row = C, groups, int(is_var), int(same_row)
+            e.count, e.eps, e.momentum = float(rpg), EPS, float(bn.momentum or 0.1)
+            n += 1
+        put(net.in_bn, self.bps_stat[0].data_ptr(), self.bps_stat[1].data_ptr(), BPS, True, True)
+        for b, blk in enumerate(net.blocks):
+            put(blk.rb.bn1, net.stat1[b][0].data_ptr(), net.stat1[b][1].data_ptr(), INNER, False, False)
+            put(blk.rb.bn2, net.stat2[b][0].data_ptr(), net.stat2[b][1].data_ptr(), HID, False, False)
+        _native.check(_L().dexgg_bn_running_multi(ents, n, _st(self.dev)))
+
+    def backward_blocks(self, net, R, groups, xhat, last, want_wgrad, want_tail_grad, drops=None):
+        """last: ('rank1', dl, w, dw_out) or ('mat', tensor, ld) - the gradient wrt the last block's output."""
+        rpg = R // groups
+        nb = len(net.blocks)
+        if want_wgrad:
+            net.db13.zero_()
+        g_src = last
+        for b in range(nb - 1, -1, -1):
+            blk, rb = net.blocks[b], net.blocks[b].rb
+            out, ldo = (net.XT[b + 1], LDXT) if b + 1 < nb else (net.Xlast, HID)
+            kw = dict(g=g_src[1].data_ptr(), ldg=g_src[2]) if g_src[0] == "mat" else dict(rank1=(g_src[1], g_src[2], g_src[3]))
+            self._bn_bwd(HID, rpg, groups, rb.bn2, net.stat2[b], net.Y[b].data_ptr(), HID, out.data_ptr(), ldo, net.GY.data_ptr(), HID,
+                         skip=net.T[b][:, INNER:].data_ptr(), lds=NCAT, gskip=net.G13[:, INNER:].data_ptr(), ldgs=NCAT,
+                         dbias_skip=net.db13[b][INNER:].data_ptr(), want_wgrad=want_wgrad, drop=(drops[b] if drops else None), **kw)
+            if want_wgrad:  # dW2 = GY^T . H  (both operands MN-major, contraction over the rows split over CTAs)
+                self._gemm(HID, INNER, [(net.GY.data_ptr(), HID, 1, net.H[b].data_ptr(), INNER, 1, R)], C32=rb.fc2.weight.grad, ldc=INNER,
+                           split_k=max(1, min(32, R // 256)))
+            self._gemm(R, INNER, [(net.GY.data_ptr(), HID, 0, blk.W2.data_ptr(), INNER, 1, HID)], C16=net.GH, ldc=INNER)
+            self._bn_bwd(INNER, rpg, groups, rb.bn1, net.stat1[b], net.T[b].data_ptr(), NCAT, net.H[b].data_ptr(), INNER, net.G13.data_ptr(), NCAT,
+                         g=net.GH.data_ptr(), ldg=INNER, want_wgrad=want_wgrad)
+            xin, ldx, K2 = self._block_in(net, b)
+            if want_wgrad:  # gradients wrt the folded first-layer weights: [768, 4096] and [768, X | tail]
+                self._gemm(NCAT, BPS, [(net.G13.data_ptr(), NCAT, 1, xhat.data_ptr(), BPS, 1, R)], C32=blk.dWb, ldc=BPS)
+                self._gemm(NCAT, blk.ldxt, [(net.G13.data_ptr(), NCAT, 1, xin.data_ptr(), ldx, 1, R)], C32=blk.dWxt, ldc=blk.ldxt)
+            if b > 0 or want_tail_grad:
+                self._gemm(R, blk.ldxt, [(net.G13.data_ptr(), NCAT, 0, blk.Wxt.data_ptr(), blk.ldxt, 1, NCAT)], C16=net.gXT[b], ldc=blk.ldxt)
+                g_src = ("mat", net.gXT[b], blk.ldxt)
+
+    def _score_head(self, net, R, groups, targets=(0.0, 0.0), dscale=(0.0, 0.0), lscale=(0.0, 0.0), labels=None, loss_slot=0, want_db=True):
+        a = ScoreHead()
+        a.X, a.ldx = net.Xlast.data_ptr(), HID
+        a.w, a.b = net.head.weight.data_ptr(), net.head.bias.data_ptr()
+        a.rows_per_group, a.n_groups = R // groups, groups
+        a.labels = labels.data_ptr() if labels is not None else None
+        for i in range(2):
+            a.target[i], a.dscale[i], a.lscale[i] = targets[i], dscale[i], lscale[i]
+        a.p, a.dl, a.loss = net.p.data_ptr(), net.dl.data_ptr(), self.loss[loss_slot:].data_ptr()
+        a.db = net.head.bias.grad.data_ptr() if want_db else None
+        a.wass = 0
+        _native.check(_L().dexgg_score_head(ctypes.byref(a), _st(self.dev)))
+
+    # ------------------------------------------------------------------------------------------------ the steps
+    def _input_norm(self, bps):
+        B = self.B
+        assert bps.shape == (B, BPS) and bps.dtype == torch.float32 and bps.is_contiguous() and bps.is_cuda
+        s = self.bps_stat
+        _native.check(_L().dexgg_bn_input_stats(bps.data_ptr(), BPS, B, BPS, EPS, s[0].data_ptr(), s[1].data_ptr(), s[2].data_ptr(), _st(self.dev)))
+        _native.check(_L().dexgg_xhat(bps.data_ptr(), BPS, s[0].data_ptr(), s[2].data_ptr(), B, BPS, self.xhat.data_ptr(), 2, _st(self.dev)))
+
+    def _dev_batch(self, data, keys):
+        out = {}
+        for k in keys:
+            v = data[k]
+            v = v if torch.is_tensor(v) else torch.as_tensor(v)
+            v = v.to(self.dev, non_blocking=True)
+            if k == "bps_object" or v.dtype not in (torch.float32, torch.float64):
+                v = v.float()
+            out[k] = v.contiguous()
+        return out
+
+    def gan_step(self, real_data, is_train_gen, Zgen):
+        m, B, dev = self.model, self.B, self.dev
+        G, D = self.G, self.D
+        d = self._dev_batch(real_data, ("bps_object", "rot_matrix", "transl", "joint_conf"))
+        real_tail = [d["rot_matrix"].reshape(B, 9), d["transl"], d["joint_conf"]]
+        self.loss.zero_()
+        G.attach()
+        D.attach()
+        with torch.cuda.device(dev), torch.no_grad():
+            self._input_norm(d["bps_object"])
+            # ---- generator forward (dexgangrasp.py:772-776) ----
+            self.prep(G)
+            self._tail_pack(G, [Zgen.float().contiguous()], 0, B, 0)
+            self.forward_blocks(G, B, 1, self.xhat)
+            self._gemm(B, self.nJ + 9, [(G.Xlast.data_ptr(), HID, 0, self.Wh.data_ptr(), HID, 0, HID)], bias=self.bh, C32=self.OUT, ldc=32)
+            _native.check(_L().dexgg_gen_pose(self.OUT.data_ptr(), 32, self.nJ, B, self.fake_rot.data_ptr(), self.fake_transl.data_ptr(),
+                                              self.fake_joint.data_ptr(), _st(dev)))
+            self.running_update(G, 1, B)
+            fake_tail = [self.fake_rot, self.fake_transl, self.fake_joint]
+            # ---- discriminator step: real | fake as one double batch with per-half statistics (:788-794) ----
+            self.prep(D)
+            self._tail_pack(D, real_tail, 0, B, 0)
+            self._tail_pack(D, fake_tail, B, B, 1)
+            self.forward_blocks(D, 2 * B, 2, self.xhat)
+            D.flat_grad.zero_()
+            bw = self.bw
+            self._score_head(D, 2 * B, 2, targets=(1.0, 0.0), dscale=(0.5 * bw / B, 0.5 * bw / B), lscale=(bw / B, bw / B), loss_slot=0)
+            self.running_update(D, 2, B)
+            self.backward_blocks(D, 2 * B, 2, self.xhat, ("rank1", D.dl, D.head.weight, D.head.weight.grad), True, False)
+            self.unfold(D)
+            m._sync_grads(D.module)
+            D.optimizer.step()
+            if is_train_gen:
+                # ---- generator step: D(fake) with the updated discriminator, gradients back into the generator (:796-816) ----
+                self.prep(D)
+                self._tail_pack(D, fake_tail, 0, B, 0)
+                self.forward_blocks(D, B, 1, self.xhat)
+                self._score_head(D, B, 1, targets=(1.0, 0.0), dscale=(bw / B, 0.0), lscale=(bw / B, 0.0), loss_slot=2, want_db=False)
+                self.running_update(D, 1, B)
+                self.backward_blocks(D, B, 1, self.xhat, ("rank1", D.dl, D.head.weight, None), False, True)
+                src = self._tail_src(fake_tail)
+                st = D.tail_stat[0]
+                _native.check(_L().dexgg_tail_bn_bwd(ctypes.byref(src), B, float(B), st[0].data_ptr(), st[1].data_ptr(), D.gXT[0].data_ptr(), TAILW, 0,
+                                                     D.gXT[1].data_ptr(), LDXT, HID, self.gPose.data_ptr(), 0, None, _st(dev)))
+                G.flat_grad.zero_()
+                self.dWh.zero_()
+                self.dbh.zero_()
+                rsrc = self._tail_src(real_tail)
+                _native.check(_L().dexgg_gen_loss(self.OUT.data_ptr(), 32, self.nJ, B, float(B), ctypes.byref(rsrc), self.gPose.data_ptr(),
+                                                  float(m.transl_coef), float(m.rot_coef), float(m.conf_coef), self.gHeads.data_ptr(), 32,
+                                                  self.loss[3:].data_ptr(), self.dbh.data_ptr(), _st(dev)))
+                self._gemm(32, HID, [(self.gHeads.data_ptr(), 32, 1, G.Xlast.data_ptr(), HID, 1, B)], C32=self.dWh, ldc=HID, split_k=max(1, min(32, B // 256)))
+                self._gemm(B, HID, [(self.gHeads.data_ptr(), 32, 0, self.Wh.data_ptr(), HID, 1, 32)], C16=self.gX, ldc=HID)
+                self.backward_blocks(G, B, 1, self.xhat, ("mat", self.gX, HID), True, False)
+                self.unfold(G)
+                m._sync_grads(G.module)
+                G.optimizer.step()
+            vals = self.mix @ self.loss
+        out = {"total_loss_disc": vals[0], "bce_loss_real": vals[1], "bce_loss_fake": vals[2]}
+        if is_train_gen:
+            gen = {"gen_loss_fake": vals[3], "transl_loss": vals[4], "rot_loss": vals[5], "conf_loss": vals[6], "total_loss_gen": vals[7]}
+            m.last_loss_dict_gen = gen
+        out.update(m.last_loss_dict_gen)
+        self._bump_versions(self.G, self.D)
+        return out
+
+    def evaluator_step(self, data):
+        m, B, dev = self.model, self.B, self.dev
+        E = self.E
+        d = self._dev_batch(data, ("bps_object", "rot_matrix", "transl", "label"))
+        m.DexEvaluator.gt_label = d["label"].float().unsqueeze(-1)
+        masks = getattr(m.DexEvaluator, "dropout_masks", None)
+        p = float(m.DexEvaluator.dout.p)
+        drops = [((masks[i] if masks is not None else None), (0.0 if masks is not None else p), i) for i in range(3)]
+        if masks is None and p <= 0.0:
+            drops = None
+        self.loss[6:7].zero_()
+        E.attach()
+        with torch.cuda.device(dev), torch.no_grad():
+            _native.check(_L().dexgg_bump_counter(self.seed.data_ptr(), _st(dev)))
+            self._input_norm(d["bps_object"])
+            self.prep(E)
+            self._tail_pack(E, [d["rot_matrix"].reshape(B, 9), d["transl"]], 0, B, 0)
+            self.forward_blocks(E, B, 1, self.xhat, drops)
+            E.flat_grad.zero_()
+            bw = self.bw
+            lab = m.DexEvaluator.gt_label.reshape(-1).contiguous()
+            self._score_head(E, B, 1, labels=lab, dscale=(bw / B, 0.0), lscale=(bw / B, 0.0), loss_slot=6)
+            self.running_update(E, 1, B)
+            self.backward_blocks(E, B, 1, self.xhat, ("rank1", E.dl, E.head.weight, E.head.weight.grad), True, False, drops)
+            self.unfold(E)
+            m._sync_grads(E.module)
+            E.optimizer.step()
+            val = self.loss[6].clone()
+        self._bump_versions(self.E)
+        return {"total_loss_eva": val, "bce_loss": val}
+
+    def _bump_versions(self, *nets):
+        """Buffers were written through raw pointers: tell torch (the packed eval-mode weights key on the version counters)."""
+        ts = []
+        for n in nets:
+            ts += [b for b in n.module.buffers() if b.is_floating_point()]
+        torch.autograd.graph.increment_version(ts)

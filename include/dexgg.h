@@ -203,6 +203,127 @@ typedef struct {
 } dexgg_gemm;
 int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Fused non-GEMM kernels of the bf16 training step (csrc/train_fused.cu; driven by dex_gan_grasp_b200/train_engine.py).
+ * They replace the ATen kernels autograd runs for nn.BatchNorm1d / LeakyReLU / Dropout / torch.cat / BCELoss / MSELoss /
+ * rot_matrix_from_ortho6d forward AND backward in DexGanGrasp.update_dexgangrasp / update_dexevaluator
+ * (models/dexgangrasp.py:739-823; networks.py:43-56, 88-103, 148-159, 315-337; losses.py:61-76).  All matrices bf16 unless noted,
+ * row pitches (ld, elements) multiples of 8; statistics, losses and parameter gradients fp32.
+ * ---------------------------------------------------------------------------------------------------------- */
+/* Train-mode BatchNorm1d forward as ONE column-slab kernel: batch statistics of x per group of rows_per_group rows (the
+ * discriminator's real and fake batches are two groups of one call), y = [dropout] LeakyReLU(gamma * xhat + beta [+ residual]).
+ * mode 0: fused.  Data parallel: mode 1 writes the local (mean, M2) to stat_out [n_groups,2,C]; after the exchange +
+ * dexgg_bn_merge, mode 2 applies with mean / invstd given.  Dropout: drop_mask (fp32, pre-scaled keep mask) or, if NULL and
+ * drop_p > 0, a counter-based Bernoulli mask from *drop_seed and drop_stream (the backward regenerates it). */
+typedef struct {
+    const void* x; int64_t ldx;
+    int C; int64_t rows_per_group; int n_groups;
+    const float* gamma; const float* beta;
+    float* mean; float* invstd;          /* [n_groups, C] saved for the backward */
+    float eps; float count_total;        /* rows of a group over ALL ranks (0: rows_per_group) */
+    const void* residual; int64_t ldr;
+    int act;
+    const float* drop_mask; int64_t ldm; float drop_p; const unsigned long long* drop_seed; unsigned drop_stream;
+    void* y; int64_t ldy;
+    int mode; float* stat_out;
+} dexgg_bn_fwd;
+int dexgg_bn_fwd_slab(const dexgg_bn_fwd* args, void* stream);
+
+/* Its backward: g_v = g [* dropout] * LeakyReLU'(out);  dgamma += sum g_v xhat;  dbeta += sum g_v;
+ * gx = gamma invstd (g_v - mean(g_v) - xhat mean(g_v xhat));  gskip = g_v * LeakyReLU'(skip), dbias_skip += sum gskip.
+ * The incoming gradient is a matrix g or the rank-1 form dl[m] * w[c] of a score head (then dw_out += sum_m dl[m] out[m,:]). */
+typedef struct {
+    const void* g; int64_t ldg;
+    const float* dl; const float* w; float* dw_out;
+    const void* out; int64_t ldo; int act;
+    const float* drop_mask; int64_t ldm; float drop_p; const unsigned long long* drop_seed; unsigned drop_stream;
+    const void* x; int64_t ldx;
+    const float* mean; const float* invstd; const float* gamma;
+    int C; int64_t rows_per_group; int n_groups; float count_total;
+    float* dgamma; float* dbeta;
+    void* gx; int64_t ldgx;
+    const void* skip; int64_t lds; void* gskip; int64_t ldgs; float* dbias_skip;
+    int mode; float* sums;               /* data parallel: 1 = local column sums -> sums [n_groups,2,C]; 2 = apply with global sums */
+} dexgg_bn_bwd;
+int dexgg_bn_bwd_slab(const dexgg_bn_bwd* args, void* stream);
+
+/* Input BatchNorm over the BPS columns, shared by the three networks of a step: statistics of x f32 [B,C], then
+ * xhat = (x - mean) * invstd as bf16 [copies * B, C] (gamma / beta are folded into the first-layer weights). */
+int dexgg_bn_input_stats(const float* x, int64_t ldx, int64_t B, int C, float eps, float* mean, float* var, float* invstd, void* stream);
+int dexgg_xhat(const float* x, int64_t ldx, const float* mean, const float* invstd, int64_t B, int C, void* out_bf16, int copies,
+               void* stream);
+
+/* The per-row inputs that are not BPS ("tail": rot 9 | transl 3 | joint nJ, or z): up to three column blocks, f32 or f64. */
+typedef struct {
+    const void* p[3];
+    int n[3];
+    int f64;
+} dexgg_tail_src;
+/* bn 1: train-mode BatchNorm statistics per tail column, normalised value (no gamma / beta) written as bf16 to up to three
+ * destinations (dst[i] + r*dst_ld[i] + dst_col0[i] + j), running statistics of those columns updated;  bn 0: plain copy. */
+int dexgg_tail_pack(const dexgg_tail_src* src, int64_t B, int bn, float eps, float count_total, float momentum, float* mean,
+                    float* invstd, float* running_mean, float* running_var, void* const* dst, const int64_t* dst_ld,
+                    const int* dst_col0, int mode, float* stat, void* stream);
+/* gradient wrt the raw tail inputs from the gradient wrt the normalised columns (gA[:, a0 + j] + gB[:, b0 + j]) -> out f32 [B,T] */
+int dexgg_tail_bn_bwd(const dexgg_tail_src* src, int64_t B, float count_total, const float* mean, const float* invstd, const void* gA,
+                      int64_t lda, int a0, const void* gB, int64_t ldb, int b0, float* out, int mode, float* sums, void* stream);
+
+/* Score head + loss (out_success + sigmoid + BCELoss, networks.py:158,336; dexgangrasp.py:142-147,213-232,293):
+ * p = sigmoid(X . w + b) over K = 512; target labels[row] or target[group]; loss[group] += lscale[group] * BCE; dl[row] =
+ * dscale[group] * (p - t); db += sum dl.  wass 1: loss = lscale * p, dl = dscale * p (1 - p) (dexgangrasp.py:204-218,258). */
+typedef struct {
+    const void* X; int64_t ldx;
+    const float* w; const float* b;
+    int64_t rows_per_group; int n_groups;
+    const float* labels;
+    float target[2], dscale[2], lscale[2];
+    float* p; float* dl; float* loss; float* db;
+    int wass;
+} dexgg_score_head_args;
+int dexgg_score_head(const dexgg_score_head_args* args, void* stream);
+
+/* Generator heads (joint nJ | rot6d 6 | transl 3, f32 [B,ldo]) -> fake grasp (rot [B,9] by Gram-Schmidt, transl, joint), and
+ * the generator's reconstruction losses + gradient wrt the heads (dexgangrasp.py:272-307, losses.py:61-76, utils.py:380-394). */
+int dexgg_gen_pose(const float* out, int64_t ldo, int n_joints, int64_t B, float* rot, float* transl, float* joint, void* stream);
+int dexgg_gen_loss(const float* out, int64_t ldo, int n_joints, int64_t B, float n_total, const dexgg_tail_src* real, const float* g_pose,
+                   float c_transl, float c_rot, float c_joint, void* g_heads, int64_t ldg, float* loss, float* dbias, void* stream);
+
+/* fp32 master weights -> bf16 GEMM operands (input BatchNorm gamma / beta folded into the first layers), and the gradients of
+ * the folded weights back to the .grad tensors of fc1 / fc3 and of the input BatchNorm. */
+typedef struct {
+    const float *W1, *W3, *b1, *b3; int Fin;
+    const int *cmap, *dmap;
+    const float *in_gamma, *in_beta;
+    void *Wb, *Wxt; int ldxt; float* bias13;
+    const float *dWb, *dWxt, *db13;
+    float *gW1, *gW3, *gb1, *gb3, *g_in_gamma, *g_in_beta;
+} dexgg_first_layer;
+typedef struct {
+    const float* src; int64_t lds; int rows, cols; void* dst; int64_t ldd;
+    const float* gsrc; int64_t ldgs; float* gdst; int64_t ldgd;
+} dexgg_plain_job;
+typedef struct {
+    int n_first, n_plain;
+    dexgg_first_layer first[3];
+    dexgg_plain_job plain[8];
+} dexgg_weight_jobs;
+int dexgg_prep_weights(const dexgg_weight_jobs* jobs, void* stream);
+int dexgg_unfold_grads(const dexgg_weight_jobs* jobs, void* stream);
+
+/* nn.BatchNorm1d buffer updates (running_mean / running_var / num_batches_tracked) of every BatchNorm of a network pass. */
+typedef struct {
+    float *running_mean, *running_var;
+    const float *mean, *second;
+    long long* num_batches_tracked;
+    int C, n_groups, second_is_var, same_row;
+    float count, eps, momentum;
+} dexgg_run_entry;
+int dexgg_bn_running_multi(const dexgg_run_entry* entries, int n, void* stream);
+/* data parallel: merge per-rank (mean, M2) [world, n_sets, 2, C] with Chan's formula */
+int dexgg_bn_merge(const float* gathered, int world, int n_sets, int C, float n_local, float eps, float* mean, float* invstd, float* var,
+                   void* stream);
+int dexgg_bump_counter(unsigned long long* counter, void* stream);
+
 int dexgg_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream);
 int dexgg_f32_to_bf16_t(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int cols, void* stream);
 
