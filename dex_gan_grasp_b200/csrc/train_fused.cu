@@ -55,7 +55,7 @@ __device__ __forceinline__ float drop_scale(unsigned long long seed, unsigned st
 }
 
 // Sum NQ x 8 per-thread values over the 128 row lanes of a 256-thread slab CTA (thread t: column half t & 1, row lane t >> 1).
-// Result for this thread's own 8 columns in `acc` on return.
+// Result for this thread's own 8 columns in `acc` on return (valid in every thread).
 template <int NQ>
 __device__ __forceinline__ void slab_reduce(float (&acc)[NQ][8], float* sm /* [8 warps][2][NQ][8] + [2][NQ][8] */) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = threadIdx.x & 1;
@@ -90,33 +90,61 @@ __device__ __forceinline__ void slab_reduce(float (&acc)[NQ][8], float* sm /* [8
         for (int j = 0; j < 8; ++j) acc[q][j] = out[(sub * NQ + q) * 8 + j];
 }
 
+// Barrier over all CTAs of a slab kernel.  The grids are sized to at most one CTA per SM (128 - 148 CTAs of 256 threads, a few
+// KB of shared memory), launched stream-ordered behind their producer, so every CTA is resident when the first one arrives.
+// bar[0] = arrival counter (reset by the last arriver), bar[1] = generation.
+__device__ __forceinline__ void slab_grid_barrier(unsigned* bar, unsigned nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned gen = *reinterpret_cast<volatile unsigned*>(bar + 1);
+        if (atomicAdd(bar, 1u) == nblocks - 1) {
+            *reinterpret_cast<volatile unsigned*>(bar) = 0u;
+            __threadfence();
+            atomicAdd(bar + 1, 1u);
+        } else {
+            while (*reinterpret_cast<volatile unsigned*>(bar + 1) == gen) __nanosleep(40);
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 // ------------------------------------------------------------------------------------------------ BatchNorm forward slab
+// grid (C / 16 column slabs, row splits, n_groups): a CTA owns 16 columns x one row range of one batch group.  Pass 1 adds the
+// CTA's shifted partial sums (shift = the layer's running mean: common to every CTA and every rank) to acc [n_groups, 2, C];
+// after the grid barrier every CTA derives mean / invstd and normalises its rows (pass 2).
 struct BnFwd {
     const __nv_bfloat16* x; int64_t ldx;
     int C; int64_t rpg; int n_groups;
-    const float *gamma, *beta;
+    const float *gamma, *beta, *shift;
     float *mean, *invstd;          // [n_groups, C]
     float eps, count;              // count = rows per group over all ranks
     const __nv_bfloat16* res; int64_t ldr;
     int act;
     const float* mask; int64_t ldm; float drop_p; const unsigned long long* seed; unsigned stream;
     __nv_bfloat16* y; int64_t ldy;
-    int mode;                      // 0 fused, 1 statistics only -> stat [n_groups, 2, C] (local mean, M2), 2 apply (mean / invstd given)
-    float* stat;
+    int mode;                      // 0 fused, 1 partial sums only (data parallel: allreduce acc, then mode 2), 2 apply from acc
+    float* acc;                    // [n_groups, 2, C] zeroed by the caller
+    unsigned* bar;
 };
 
 __global__ void __launch_bounds__(256) bn_fwd_slab_kernel(const BnFwd a) {
     __shared__ float sm[8 * 2 * 2 * 8 + 2 * 2 * 8];
-    const int sub = threadIdx.x & 1, rl = threadIdx.x >> 1, g = blockIdx.y;
+    const int sub = threadIdx.x & 1, rl = threadIdx.x >> 1, g = blockIdx.z;
     const int c0 = blockIdx.x * 16 + sub * 8;
-    const int64_t r0 = (int64_t)g * a.rpg, r1 = r0 + a.rpg;
-    float mean[8], istd[8];
+    const int64_t chunk = ((a.rpg + gridDim.y - 1) / gridDim.y + 127) / 128 * 128;
+    const int64_t g0 = (int64_t)g * a.rpg;
+    const int64_t r0 = g0 + (int64_t)blockIdx.y * chunk, r1 = (r0 + chunk < g0 + a.rpg) ? r0 + chunk : g0 + a.rpg;
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = a.shift ? a.shift[c0 + j] : 0.f;
+    float* accg = a.acc + (int64_t)g * 2 * a.C;
     if (a.mode != 2) {
-        float s[8];
-        unpack8(ld8(a.x + r0 * a.ldx + c0), s);  // shift: the group's first row (keeps the one-pass variance well conditioned)
         float acc[2][8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = 0.f;
+#pragma unroll 4
         for (int64_t r = r0 + rl; r < r1; r += 128) {
             float v[8];
             unpack8(ld8(a.x + r * a.ldx + c0), v);
@@ -128,39 +156,32 @@ __global__ void __launch_bounds__(256) bn_fwd_slab_kernel(const BnFwd a) {
             }
         }
         slab_reduce<2>(acc, sm);
-        const float n = (float)a.rpg;
+        if (rl == 0 && r0 < r1) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            mean[j] = s[j] + acc[0][j] / n;
-            const float m2 = fmaxf(acc[1][j] - acc[0][j] * acc[0][j] / n, 0.f);
-            if (a.mode == 1) {
-                if (rl == 0) {
-                    a.stat[((int64_t)g * 2 + 0) * a.C + c0 + j] = mean[j];
-                    a.stat[((int64_t)g * 2 + 1) * a.C + c0 + j] = m2;
-                }
-            } else {
-                istd[j] = rsqrtf(m2 / n + a.eps);
-                if (rl == 0) {
-                    a.mean[(int64_t)g * a.C + c0 + j] = mean[j];
-                    a.invstd[(int64_t)g * a.C + c0 + j] = istd[j];
-                }
+            for (int j = 0; j < 8; ++j) {
+                atomicAdd(accg + c0 + j, acc[0][j]);
+                atomicAdd(accg + a.C + c0 + j, acc[1][j]);
             }
         }
         if (a.mode == 1) return;
-    } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            mean[j] = a.mean[(int64_t)g * a.C + c0 + j];
-            istd[j] = a.invstd[(int64_t)g * a.C + c0 + j];
-        }
+        slab_grid_barrier(a.bar, gridDim.x * gridDim.y * gridDim.z);
     }
     float sc[8], sh[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        sc[j] = a.gamma[c0 + j] * istd[j];
-        sh[j] = a.beta[c0 + j] - mean[j] * sc[j];
+        const float sd = __ldcg(accg + c0 + j), sq = __ldcg(accg + a.C + c0 + j);
+        const float mean = s[j] + sd / a.count;
+        const float var = fmaxf(sq / a.count - (sd / a.count) * (sd / a.count), 0.f);
+        const float istd = rsqrtf(var + a.eps);
+        if (rl == 0 && blockIdx.y == 0) {
+            a.mean[(int64_t)g * a.C + c0 + j] = mean;
+            a.invstd[(int64_t)g * a.C + c0 + j] = istd;
+        }
+        sc[j] = a.gamma[c0 + j] * istd;
+        sh[j] = a.beta[c0 + j] - mean * sc[j];
     }
     const unsigned long long seed = (a.drop_p > 0.f && !a.mask && a.seed) ? *a.seed : 0ull;
+#pragma unroll 2
     for (int64_t r = r0 + rl; r < r1; r += 128) {
         float v[8];
         unpack8(ld8(a.x + r * a.ldx + c0), v);
@@ -203,15 +224,18 @@ struct BnBwd {
     const __nv_bfloat16* skip; int64_t lds;     // skip-branch activation (post-LeakyReLU) or NULL
     __nv_bfloat16* gskip; int64_t ldgs;         // out: g * LeakyReLU'(skip)
     float* dbias_skip;                          // [C] += sum_m gskip (may be NULL)
-    int mode;                                   // 0 fused, 1 column sums only -> sums [n_groups, 2, C], 2 apply with global sums given
-    float* sums;
+    int mode;                                   // 0 fused, 1 column sums only (data parallel: allreduce acc, then mode 2), 2 apply from acc
+    float* acc;                                 // [n_groups, 2, C] zeroed by the caller: sum g, sum g * xhat
+    unsigned* bar;
 };
 
 __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
     __shared__ float sm[8 * 2 * 4 * 8 + 2 * 4 * 8];
-    const int sub = threadIdx.x & 1, rl = threadIdx.x >> 1, gi = blockIdx.y;
+    const int sub = threadIdx.x & 1, rl = threadIdx.x >> 1, gi = blockIdx.z;
     const int c0 = blockIdx.x * 16 + sub * 8;
-    const int64_t r0 = (int64_t)gi * a.rpg, r1 = r0 + a.rpg;
+    const int64_t chunk = ((a.rpg + gridDim.y - 1) / gridDim.y + 127) / 128 * 128;
+    const int64_t g0 = (int64_t)gi * a.rpg;
+    const int64_t r0 = g0 + (int64_t)blockIdx.y * chunk, r1 = (r0 + chunk < g0 + a.rpg) ? r0 + chunk : g0 + a.rpg;
     float mean[8], istd[8], wv[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -244,21 +268,22 @@ __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
             }
         }
     };
-    float S[4][8];  // 0: sum g, 1: sum g * xhat, 2: sum dl * out, 3: sum gskip
+    float* accg = a.acc + (int64_t)gi * 2 * a.C;
     if (a.mode != 2) {
+        float S[4][8];  // 0: sum g, 1: sum g * xhat, 2: sum dl * out, 3: sum gskip
 #pragma unroll
         for (int q = 0; q < 4; ++q)
 #pragma unroll
             for (int j = 0; j < 8; ++j) S[q][j] = 0.f;
+#pragma unroll 2
         for (int64_t r = r0 + rl; r < r1; r += 128) {
             float gv[8], ov[8], xv[8];
-            if (!a.g && a.out) {  // rank-1 form: dw_out uses the saved output BEFORE the activation gradient is applied to g
-                unpack8(ld8(a.out + r * a.ldo + c0), ov);
+            grad_row(r, gv, ov);
+            if (!a.g && a.out) {  // rank-1 form: the head's weight gradient needs the saved output itself
                 const float d = a.dl[r];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) S[2][j] = fmaf(d, ov[j], S[2][j]);
             }
-            grad_row(r, gv, ov);
             unpack8(ld8(a.x + r * a.ldx + c0), xv);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -273,34 +298,28 @@ __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
             }
         }
         slab_reduce<4>(S, sm);
-        if (rl == 0) {
+        if (rl == 0 && r0 < r1) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
+                atomicAdd(accg + c0 + j, S[0][j]);
+                atomicAdd(accg + a.C + c0 + j, S[1][j]);
                 if (a.dgamma) atomicAdd(a.dgamma + c0 + j, S[1][j]);
                 if (a.dbeta) atomicAdd(a.dbeta + c0 + j, S[0][j]);
                 if (a.dw_out && !a.g) atomicAdd(a.dw_out + c0 + j, S[2][j]);
                 if (a.dbias_skip && a.skip) atomicAdd(a.dbias_skip + c0 + j, S[3][j]);
-                if (a.mode == 1) {
-                    a.sums[((int64_t)gi * 2 + 0) * a.C + c0 + j] = S[0][j];
-                    a.sums[((int64_t)gi * 2 + 1) * a.C + c0 + j] = S[1][j];
-                }
             }
         }
         if (a.mode == 1) return;
-    } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            S[0][j] = a.sums[((int64_t)gi * 2 + 0) * a.C + c0 + j];
-            S[1][j] = a.sums[((int64_t)gi * 2 + 1) * a.C + c0 + j];
-        }
+        slab_grid_barrier(a.bar, gridDim.x * gridDim.y * gridDim.z);
     }
     float k0[8], k1[8], k2[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         k0[j] = a.gamma[c0 + j] * istd[j];
-        k1[j] = S[0][j] / a.count;
-        k2[j] = S[1][j] / a.count;
+        k1[j] = __ldcg(accg + c0 + j) / a.count;
+        k2[j] = __ldcg(accg + a.C + c0 + j) / a.count;
     }
+#pragma unroll 2
     for (int64_t r = r0 + rl; r < r1; r += 128) {
         float gv[8], ov[8], xv[8], o[8];
         grad_row(r, gv, ov);
@@ -319,36 +338,50 @@ __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
 }
 
 // ------------------------------------------------------------------------------------------------ input BatchNorm (BPS columns)
-// Column statistics of the fp32 BPS batch [B, C]: a CTA owns 32 columns (32 x 8 threads), shifted single pass.
-// out: mean [C], var [C] (biased, local rows), invstd [C]
-__global__ void __launch_bounds__(256) bn_input_stats_kernel(const float* __restrict__ x, int64_t ldx, int64_t B, int C, float eps,
-                                                             float* __restrict__ mean, float* __restrict__ var, float* __restrict__ invstd) {
-    __shared__ float s0[8][33], s1[8][33];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int c = blockIdx.x * 32 + tx;
-    float a0 = 0.f, a1 = 0.f, sh = 0.f;
+// Column statistics of the fp32 BPS batch [B, C] (C % 4 == 0): grid (C / 128, row splits); a thread owns 4 adjacent columns
+// (float4 loads, a warp reads 512 contiguous bytes of a row), warps stride over the rows.  Shifted sums (shift = row 0 of the batch,
+// common to all CTAs) are added to acc [2, C] (zeroed by the caller); bn_input_finalize_kernel turns them into mean / var / invstd.
+__global__ void __launch_bounds__(256) bn_input_stats_kernel(const float* __restrict__ x, int64_t ldx, int64_t B, int C, float* __restrict__ acc) {
+    __shared__ float4 s0[8][32], s1[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c = (blockIdx.x * 32 + lane) * 4;
+    const int64_t chunk = (B + gridDim.y - 1) / gridDim.y;
+    const int64_t r0 = (int64_t)blockIdx.y * chunk, r1 = (r0 + chunk < B) ? r0 + chunk : B;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
     if (c < C) {
-        sh = x[c];
-        for (int64_t r = ty; r < B; r += 8) {
-            const float d = x[r * ldx + c] - sh;
-            a0 += d;
-            a1 = fmaf(d, d, a1);
+        const float4 sh = *reinterpret_cast<const float4*>(x + c);
+#pragma unroll 4
+        for (int64_t r = r0 + warp; r < r1; r += 8) {
+            const float4 v = *reinterpret_cast<const float4*>(x + r * ldx + c);
+            const float dx = v.x - sh.x, dy = v.y - sh.y, dz = v.z - sh.z, dw = v.w - sh.w;
+            a0.x += dx; a0.y += dy; a0.z += dz; a0.w += dw;
+            a1.x = fmaf(dx, dx, a1.x); a1.y = fmaf(dy, dy, a1.y); a1.z = fmaf(dz, dz, a1.z); a1.w = fmaf(dw, dw, a1.w);
         }
     }
-    s0[ty][tx] = a0;
-    s1[ty][tx] = a1;
+    s0[warp][lane] = a0;
+    s1[warp][lane] = a1;
     __syncthreads();
-    if (ty == 0 && c < C) {
+    if (warp == 0 && c < C) {
 #pragma unroll
         for (int j = 1; j < 8; ++j) {
-            a0 += s0[j][tx];
-            a1 += s1[j][tx];
+            const float4 p = s0[j][lane], q = s1[j][lane];
+            a0.x += p.x; a0.y += p.y; a0.z += p.z; a0.w += p.w;
+            a1.x += q.x; a1.y += q.y; a1.z += q.z; a1.w += q.w;
         }
-        const float n = (float)B, m2 = fmaxf(a1 - a0 * a0 / n, 0.f);
-        mean[c] = sh + a0 / n;
-        var[c] = m2 / n;
-        invstd[c] = rsqrtf(m2 / n + eps);
+        atomicAdd(acc + c, a0.x); atomicAdd(acc + c + 1, a0.y); atomicAdd(acc + c + 2, a0.z); atomicAdd(acc + c + 3, a0.w);
+        atomicAdd(acc + C + c, a1.x); atomicAdd(acc + C + c + 1, a1.y); atomicAdd(acc + C + c + 2, a1.z); atomicAdd(acc + C + c + 3, a1.w);
     }
+}
+// local statistics from the shifted sums: mean, biased variance, invstd, and M2 = n * var (for the cross-rank Chan merge)
+__global__ void bn_input_finalize_kernel(const float* __restrict__ x, const float* __restrict__ acc, int64_t B, int C, float eps,
+                                         float* __restrict__ mean, float* __restrict__ var, float* __restrict__ invstd) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float n = (float)B, sd = acc[c], sq = acc[C + c];
+    const float m2 = fmaxf(sq - sd * sd / n, 0.f);
+    mean[c] = x[c] + sd / n;
+    var[c] = m2 / n;
+    invstd[c] = rsqrtf(m2 / n + eps);
 }
 
 // xhat = (x - mean) * invstd as bf16 [B, C] (C % 4 == 0), written `copies` times back to back (the discriminator's real | fake
@@ -828,19 +861,31 @@ using namespace dexgg;
 
 #define TF_ST static_cast<cudaStream_t>(stream)
 
+// (column slabs, row splits, groups) with at most one CTA per SM in total: the kernels synchronise the grid with a barrier
+static dim3 slab_grid(int C, int64_t rows_per_group, int n_groups) {
+    const int slabs = C / 16;
+    int rs = sm_count() / (slabs * n_groups);
+    const int64_t max_rs = (rows_per_group + 127) / 128;
+    if (rs > max_rs) rs = (int)max_rs;
+    if (rs < 1) rs = 1;
+    return dim3(slabs, rs, n_groups);
+}
+
 extern "C" int dexgg_bn_fwd_slab(const dexgg_bn_fwd* q, void* stream) {
     DEXGG_ARCH_OK();
     DEXGG_REQUIRE(q && q->x && q->C >= 16 && q->C % 16 == 0 && q->rows_per_group >= 1 && q->n_groups >= 1 && q->ldx % 8 == 0,
                   "bn_fwd_slab: bad arguments (C %% 16 == 0, row pitches %% 8 == 0)");
     DEXGG_REQUIRE(q->mode == 1 || (q->y && q->gamma && q->beta && q->mean && q->invstd && q->ldy % 8 == 0), "bn_fwd_slab: null pointer");
+    DEXGG_REQUIRE(q->n_groups <= 2, "bn_fwd_slab: at most two batch groups");
     BnFwd a;
     a.x = static_cast<const __nv_bfloat16*>(q->x); a.ldx = q->ldx; a.C = q->C; a.rpg = q->rows_per_group; a.n_groups = q->n_groups;
-    a.gamma = q->gamma; a.beta = q->beta; a.mean = q->mean; a.invstd = q->invstd; a.eps = q->eps;
+    a.gamma = q->gamma; a.beta = q->beta; a.shift = q->shift; a.mean = q->mean; a.invstd = q->invstd; a.eps = q->eps;
     a.count = q->count_total > 0.f ? q->count_total : (float)q->rows_per_group;
     a.res = static_cast<const __nv_bfloat16*>(q->residual); a.ldr = q->ldr; a.act = q->act;
     a.mask = q->drop_mask; a.ldm = q->ldm; a.drop_p = q->drop_p; a.seed = q->drop_seed; a.stream = q->drop_stream;
-    a.y = static_cast<__nv_bfloat16*>(q->y); a.ldy = q->ldy; a.mode = q->mode; a.stat = q->stat_out;
-    bn_fwd_slab_kernel<<<dim3(q->C / 16, q->n_groups), 256, 0, TF_ST>>>(a);
+    a.y = static_cast<__nv_bfloat16*>(q->y); a.ldy = q->ldy; a.mode = q->mode; a.acc = q->acc; a.bar = q->barrier;
+    DEXGG_REQUIRE(a.acc && (q->mode != 0 || a.bar), "bn_fwd_slab: accumulator / barrier scratch missing");
+    bn_fwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_fwd_slab_kernel");
     return DEXGG_OK;
@@ -861,20 +906,26 @@ extern "C" int dexgg_bn_bwd_slab(const dexgg_bn_bwd* q, void* stream) {
     a.count = q->count_total > 0.f ? q->count_total : (float)q->rows_per_group;
     a.dgamma = q->dgamma; a.dbeta = q->dbeta; a.gx = static_cast<__nv_bfloat16*>(q->gx); a.ldgx = q->ldgx;
     a.skip = static_cast<const __nv_bfloat16*>(q->skip); a.lds = q->lds; a.gskip = static_cast<__nv_bfloat16*>(q->gskip); a.ldgs = q->ldgs;
-    a.dbias_skip = q->dbias_skip; a.mode = q->mode; a.sums = q->sums;
-    bn_bwd_slab_kernel<<<dim3(q->C / 16, q->n_groups), 256, 0, TF_ST>>>(a);
+    a.dbias_skip = q->dbias_skip; a.mode = q->mode; a.acc = q->acc; a.bar = q->barrier;
+    DEXGG_REQUIRE(a.acc && (q->mode != 0 || a.bar), "bn_bwd_slab: accumulator / barrier scratch missing");
+    bn_bwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_bwd_slab_kernel");
     return DEXGG_OK;
 }
 
 extern "C" int dexgg_bn_input_stats(const float* x, int64_t ldx, int64_t B, int C, float eps, float* mean, float* var, float* invstd,
-                                    void* stream) {
+                                    float* acc, void* stream) {
     DEXGG_ARCH_OK();
-    DEXGG_REQUIRE(x && mean && var && invstd && B >= 1 && C >= 1, "bn_input_stats: bad arguments");
-    bn_input_stats_kernel<<<nblk(C, 32), 256, 0, TF_ST>>>(x, ldx, B, C, eps, mean, var, invstd);
-    count_launches(1);
-    DEXGG_LAUNCH_OK("bn_input_stats_kernel");
+    DEXGG_REQUIRE(x && mean && var && invstd && acc && B >= 1 && C >= 4 && C % 4 == 0 && ldx % 4 == 0, "bn_input_stats: bad arguments");
+    const int gx = (C + 127) / 128;
+    int rs = 4 * sm_count() / gx;
+    if (rs > (B + 31) / 32) rs = (int)((B + 31) / 32);
+    if (rs < 1) rs = 1;
+    bn_input_stats_kernel<<<dim3(gx, rs), 256, 0, TF_ST>>>(x, ldx, B, C, acc);
+    bn_input_finalize_kernel<<<nblk(C), 256, 0, TF_ST>>>(x, acc, B, C, eps, mean, var, invstd);
+    count_launches(2);
+    DEXGG_LAUNCH_OK("bn_input_stats kernels");
     return DEXGG_OK;
 }
 

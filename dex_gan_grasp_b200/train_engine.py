@@ -182,6 +182,22 @@ class TrainEngine:
         mix[7, 2] = mix[7, 3] = mix[7, 4] = mix[7, 5] = 1.0  # total_loss_gen
         mix[8, 6] = 1.0               # total_loss_eva
         self.mix, self.bw = mix, bw
+        # per-launch accumulator slots of the column-slab kernels ([2 groups, 2, 512] floats each; the whole scratch is zeroed once
+        # at the start of a step and every launch of the step takes the next slot) + the words of their grid barrier
+        self.SLOT = 4096
+        self.scratch = torch.zeros((64 * self.SLOT,), **f32)
+        self.bar = torch.zeros((4,), dtype=torch.int32, device=dev)
+        self._slot = 0
+
+    def _next_slot(self):
+        p = self.scratch.data_ptr() + 4 * self.SLOT * self._slot
+        self._slot += 1
+        assert self._slot <= 64
+        return p
+
+    def _begin_step(self):
+        self.scratch.zero_()
+        self._slot = 0
 
     # ------------------------------------------------------------------------------------------------ kernel wrappers
     def _gemm(self, M, N, segs, bias=None, act_from=None, C16=None, C32=None, ldc=None, split_k=0, accumulate=0):
@@ -200,8 +216,9 @@ class TrainEngine:
     def _bn_fwd(self, x, ldx, C, rpg, groups, bn, stat, y, ldy, res=None, ldr=0, drop=None):
         a = BnFwd()
         a.x, a.ldx, a.C, a.rows_per_group, a.n_groups = x, ldx, C, rpg, groups
-        a.gamma, a.beta = bn.weight.data_ptr(), bn.bias.data_ptr()
+        a.gamma, a.beta, a.shift = bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr()
         a.mean, a.invstd = stat[0].data_ptr(), stat[1].data_ptr()
+        a.acc, a.barrier = self._next_slot(), self.bar.data_ptr()
         a.eps, a.count_total = EPS, float(rpg)
         a.residual, a.ldr, a.act = res, ldr, 1
         if drop is not None:
@@ -236,6 +253,7 @@ class TrainEngine:
             a.skip, a.lds, a.gskip, a.ldgs = skip, lds, gskip, ldgs
             a.dbias_skip = dbias_skip if want_wgrad else None
         a.mode = 0
+        a.acc, a.barrier = self._next_slot(), self.bar.data_ptr()
         _native.check(_L().dexgg_bn_bwd_slab(ctypes.byref(a), _st(self.dev)))
 
     @staticmethod
@@ -404,7 +422,8 @@ class TrainEngine:
         B = self.B
         assert bps.shape == (B, BPS) and bps.dtype == torch.float32 and bps.is_contiguous() and bps.is_cuda
         s = self.bps_stat
-        _native.check(_L().dexgg_bn_input_stats(bps.data_ptr(), BPS, B, BPS, EPS, s[0].data_ptr(), s[1].data_ptr(), s[2].data_ptr(), _st(self.dev)))
+        _native.check(_L().dexgg_bn_input_stats(bps.data_ptr(), BPS, B, BPS, EPS, s[0].data_ptr(), s[1].data_ptr(), s[2].data_ptr(),
+                                                self._next_slot() + 0 * self._next_slot(), _st(self.dev)))  # [2, 4096] floats = two slots
         _native.check(_L().dexgg_xhat(bps.data_ptr(), BPS, s[0].data_ptr(), s[2].data_ptr(), B, BPS, self.xhat.data_ptr(), 2, _st(self.dev)))
 
     def _dev_batch(self, data, keys):
@@ -424,6 +443,7 @@ class TrainEngine:
         d = self._dev_batch(real_data, ("bps_object", "rot_matrix", "transl", "joint_conf"))
         real_tail = [d["rot_matrix"].reshape(B, 9), d["transl"], d["joint_conf"]]
         self.loss.zero_()
+        self._begin_step()
         G.attach()
         D.attach()
         with torch.cuda.device(dev), torch.no_grad():
@@ -495,6 +515,7 @@ class TrainEngine:
         if masks is None and p <= 0.0:
             drops = None
         self.loss[6:7].zero_()
+        self._begin_step()
         E.attach()
         with torch.cuda.device(dev), torch.no_grad():
             _native.check(_L().dexgg_bump_counter(self.seed.data_ptr(), _st(dev)))

@@ -447,7 +447,7 @@ class DexggAdam(torch.optim.Adam):
     dexgg_adam_step launch over all parameters of a group.  State layout ('step', 'exp_avg', 'exp_avg_sq') and state_dict
     are torch's, so optimizer checkpoints written by the reference load unchanged."""
 
-    CHUNK = 1 << 16
+    CHUNK = 1 << 13  # elements per CTA of the fused kernel (many small CTAs keep the HBM pipes full)
     device_step = False  # True: the step count is kept in device memory too (dexgg_adam_step_dev), as CUDA-graph capture needs
 
     @torch.no_grad()

@@ -210,22 +210,26 @@ int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream);
  * (models/dexgangrasp.py:739-823; networks.py:43-56, 88-103, 148-159, 315-337; losses.py:61-76).  All matrices bf16 unless noted,
  * row pitches (ld, elements) multiples of 8; statistics, losses and parameter gradients fp32.
  * ---------------------------------------------------------------------------------------------------------- */
-/* Train-mode BatchNorm1d forward as ONE column-slab kernel: batch statistics of x per group of rows_per_group rows (the
- * discriminator's real and fake batches are two groups of one call), y = [dropout] LeakyReLU(gamma * xhat + beta [+ residual]).
- * mode 0: fused.  Data parallel: mode 1 writes the local (mean, M2) to stat_out [n_groups,2,C]; after the exchange +
- * dexgg_bn_merge, mode 2 applies with mean / invstd given.  Dropout: drop_mask (fp32, pre-scaled keep mask) or, if NULL and
+/* Train-mode BatchNorm1d forward as ONE kernel: batch statistics of x per group of rows_per_group rows (the discriminator's
+ * real and fake batches are two groups of one call), y = [dropout] LeakyReLU(gamma * xhat + beta [+ residual]).  A CTA owns
+ * 16 columns x a row range; the grid (at most one CTA per SM) meets at a barrier between the statistics pass and the apply
+ * pass.  mode 0: fused.  Data parallel: mode 1 adds the local shifted sums to acc and returns; after ONE allreduce of acc,
+ * mode 2 applies (count_total = rows of a group over all ranks).  Dropout: drop_mask (fp32, pre-scaled keep mask) or, if NULL and
  * drop_p > 0, a counter-based Bernoulli mask from *drop_seed and drop_stream (the backward regenerates it). */
 typedef struct {
     const void* x; int64_t ldx;
     int C; int64_t rows_per_group; int n_groups;
     const float* gamma; const float* beta;
+    const float* shift;                  /* [C] common shift of the one-pass variance (the layer's running mean) or NULL */
     float* mean; float* invstd;          /* [n_groups, C] saved for the backward */
     float eps; float count_total;        /* rows of a group over ALL ranks (0: rows_per_group) */
     const void* residual; int64_t ldr;
     int act;
     const float* drop_mask; int64_t ldm; float drop_p; const unsigned long long* drop_seed; unsigned drop_stream;
     void* y; int64_t ldy;
-    int mode; float* stat_out;
+    int mode;
+    float* acc;                          /* [n_groups, 2, C] scratch, ZEROED by the caller: shifted column sums */
+    unsigned* barrier;                   /* [2] grid-barrier words (mode 0), zero-initialised once */
 } dexgg_bn_fwd;
 int dexgg_bn_fwd_slab(const dexgg_bn_fwd* args, void* stream);
 
@@ -243,13 +247,16 @@ typedef struct {
     float* dgamma; float* dbeta;
     void* gx; int64_t ldgx;
     const void* skip; int64_t lds; void* gskip; int64_t ldgs; float* dbias_skip;
-    int mode; float* sums;               /* data parallel: 1 = local column sums -> sums [n_groups,2,C]; 2 = apply with global sums */
+    int mode;                            /* data parallel: 1 = local column sums into acc; 2 = apply with the (allreduced) acc */
+    float* acc;                          /* [n_groups, 2, C] scratch, ZEROED by the caller */
+    unsigned* barrier;
 } dexgg_bn_bwd;
 int dexgg_bn_bwd_slab(const dexgg_bn_bwd* args, void* stream);
 
 /* Input BatchNorm over the BPS columns, shared by the three networks of a step: statistics of x f32 [B,C], then
  * xhat = (x - mean) * invstd as bf16 [copies * B, C] (gamma / beta are folded into the first-layer weights). */
-int dexgg_bn_input_stats(const float* x, int64_t ldx, int64_t B, int C, float eps, float* mean, float* var, float* invstd, void* stream);
+int dexgg_bn_input_stats(const float* x, int64_t ldx, int64_t B, int C, float eps, float* mean, float* var, float* invstd,
+                         float* acc /* [2,C] zeroed scratch */, void* stream);
 int dexgg_xhat(const float* x, int64_t ldx, const float* mean, const float* invstd, int64_t B, int C, void* out_bf16, int copies,
                void* stream);
 
