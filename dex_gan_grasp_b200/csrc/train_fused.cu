@@ -468,9 +468,14 @@ __global__ void __launch_bounds__(256) tail_pack_kernel(const TailSrc src, int T
                 running_var[j] = (1.f - momentum) * running_var[j] + momentum * (count > 1.f ? var * (count / (count - 1.f)) : var);
             }
         }
-    } else if (bn) {
+    } else if (bn) {  // statistics merged over the ranks by the caller
         mu = mean[j];
         is = invstd[j];
+        if (threadIdx.x == 0 && running_mean) {
+            const float var = fmaxf(1.f / (is * is) - eps, 0.f);
+            running_mean[j] = (1.f - momentum) * running_mean[j] + momentum * mu;
+            running_var[j] = (1.f - momentum) * running_var[j] + momentum * (count > 1.f ? var * (count / (count - 1.f)) : var);
+        }
     }
     for (int64_t r = threadIdx.x; r < B; r += 256) {
         const __nv_bfloat16 v = __float2bfloat16_rn((tail_value(src, r, j) - mu) * is);
@@ -628,6 +633,9 @@ __global__ void __launch_bounds__(128) gen_loss_kernel(const float* __restrict__
     if (threadIdx.x < 32) s_b[threadIdx.x] = 0.f;
     __syncthreads();
     float lt = 0.f, lr = 0.f, lj = 0.f;
+    float gv[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) gv[i] = 0.f;
     const int T = 12 + nJ;
     if (m < B) {
         const float* h = out + m * ldo;
@@ -644,25 +652,39 @@ __global__ void __launch_bounds__(128) gen_loss_kernel(const float* __restrict__
         }
         V3 ga, gb;
         rot6d_columns_bwd(a, b, V3{gR[0], gR[3], gR[6]}, V3{gR[1], gR[4], gR[7]}, V3{gR[2], gR[5], gR[8]}, ga, gb);
-        __nv_bfloat16* go = g_heads + m * ldg;
-        float gv[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) gv[i] = 0.f;
-        for (int j = 0; j < nJ; ++j) {
-            const float d = h[j] - tail_value(real, m, 12 + j);
-            lj = fmaf(d, d, lj);
-            gv[j] = c_j * 2.f * d / ((float)nJ * n_total) + (g_pose ? g_pose[m * T + 12 + j] : 0.f);
+        for (int j = 0; j < 20; ++j) {
+            if (j < nJ) {
+                const float d = h[j] - tail_value(real, m, 12 + j);
+                lj = fmaf(d, d, lj);
+                gv[j] = c_j * 2.f * d / ((float)nJ * n_total) + (g_pose ? g_pose[m * T + 12 + j] : 0.f);
+            }
         }
-        gv[nJ] = ga.x; gv[nJ + 1] = ga.y; gv[nJ + 2] = ga.z; gv[nJ + 3] = gb.x; gv[nJ + 4] = gb.y; gv[nJ + 5] = gb.z;
+        const float g6[6] = {ga.x, ga.y, ga.z, gb.x, gb.y, gb.z};
+        float g3[3];
+#pragma unroll
         for (int j = 0; j < 3; ++j) {
             const float d = h[nJ + 6 + j] - tail_value(real, m, 9 + j);
             lt = fmaf(d, d, lt);
-            gv[nJ + 6 + j] = c_t * 2.f * d / (3.f * n_total) + (g_pose ? g_pose[m * T + 9 + j] : 0.f);
+            g3[j] = c_t * 2.f * d / (3.f * n_total) + (g_pose ? g_pose[m * T + 9 + j] : 0.f);
         }
-        for (int i = 0; i < 32 && i < ldg; ++i) {
-            go[i] = __float2bfloat16_rn(gv[i]);
-            if (i < nJ + 9) atomicAdd(&s_b[i], gv[i]);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {  // static indexing keeps gv in registers
+            if (i >= nJ && i < nJ + 6) gv[i] = g6[i - nJ];
+            if (i >= nJ + 6 && i < nJ + 9) gv[i] = g3[i - nJ - 6];
         }
+        __nv_bfloat16* go = g_heads + m * ldg;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+            if (i < ldg) go[i] = __float2bfloat16_rn(gv[i]);
+    }
+    // head-bias gradients = column sums of gv: over the warp's 32 rows first, then one shared atomic per warp and column
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        float v = gv[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && i < nJ + 9) atomicAdd(&s_b[i], v);
     }
     lt *= c_t / (3.f * n_total);
     lr *= c_r / (9.f * n_total);

@@ -33,6 +33,13 @@ def all_reduce_sum(t, kind="grad", async_op=False):
     return dist.all_reduce(t, op=dist.ReduceOp.SUM, async_op=async_op)
 
 
+def all_gather(out, t, kind="bn_fwd"):
+    """out [world, ...] <- every rank's t"""
+    _COUNTERS[kind + "_calls"] += 1
+    _COUNTERS[kind + "_bytes"] += out.numel() * out.element_size()
+    return dist.all_gather_into_tensor(out, t)
+
+
 def allreduce_gradients(module):
     """Average the gradients of `module` over all ranks with a single flat allreduce."""
     if not is_parallel():

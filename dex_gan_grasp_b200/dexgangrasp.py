@@ -447,11 +447,9 @@ class DexGanGrasp(object):
                 else "autograd Functions over the dexgg kernels (train_ops.py)")
 
     def _use_engine(self):
-        """The fused bf16 step (train_engine.py) runs the BCE variant on one rank; the WGAN-GP variant, the fp32 parity mode and
-        cfg['train_engine'] = False use the autograd-Function path of train_ops.py."""
-        from . import dataparallel
-        return (self.cfg.get("precision", "fp32") == "bf16" and not self.is_wgan and self.cfg.get("train_engine", True)
-                and not dataparallel.is_parallel())
+        """The fused bf16 step (train_engine.py) runs the BCE variant (any number of ranks); the WGAN-GP variant, the fp32 parity
+        mode and cfg['train_engine'] = False use the autograd-Function path of train_ops.py."""
+        return self.cfg.get("precision", "fp32") == "bf16" and not self.is_wgan and self.cfg.get("train_engine", True)
 
     def _engine(self, rows):
         from .train_engine import TrainEngine

@@ -83,7 +83,15 @@ class _Net:
         self.G13 = torch.zeros((R, NCAT), **bf)
         self.gXT = [torch.zeros((R, TAILW), **bf)] + [torch.zeros((R, LDXT), **bf) for _ in range(nb - 1)]
         self.tail_stat = torch.zeros((groups, 2, TAILW), **f32)  # per group: mean | invstd of the tail columns
-        self.db13 = torch.zeros((nb, NCAT), **f32)  # column sums of the first-layer output gradient (fc3 part), zeroed per backward
+        # column sums of the first-layer output gradient (fc3 part) and the gradients of the [X | tail] weight columns: one flat
+        # scratch zeroed once per backward (bias sums and split contractions accumulate with atomics)
+        n_small = nb * NCAT + sum(NCAT * blk.ldxt for blk in blocks)
+        self.small_scratch = torch.zeros((n_small,), **f32)
+        self.db13 = self.small_scratch[:nb * NCAT].view(nb, NCAT)
+        off = nb * NCAT
+        for blk in blocks:
+            blk.dWxt = self.small_scratch[off:off + NCAT * blk.ldxt].view(NCAT, blk.ldxt)
+            off += NCAT * blk.ldxt
         self.dl = torch.zeros((R,), **f32)
         self.p = torch.zeros((R,), **f32)
         # flat gradient buffer; every parameter's .grad is a view into it (one memset to zero, one allreduce to exchange)
@@ -185,15 +193,35 @@ class TrainEngine:
         # per-launch accumulator slots of the column-slab kernels ([2 groups, 2, 512] floats each; the whole scratch is zeroed once
         # at the start of a step and every launch of the step takes the next slot) + the words of their grid barrier
         self.SLOT = 4096
+        self.world = _world()
         self.scratch = torch.zeros((64 * self.SLOT,), **f32)
         self.bar = torch.zeros((4,), dtype=torch.int32, device=dev)
         self._slot = 0
 
-    def _next_slot(self):
-        p = self.scratch.data_ptr() + 4 * self.SLOT * self._slot
-        self._slot += 1
+    def _next_slot(self, n=1):
+        """index of the next `n` free accumulator slots of this step"""
+        i = self._slot
+        self._slot += n
         assert self._slot <= 64
-        return p
+        return i
+
+    def _slot_ptr(self, i):
+        return self.scratch.data_ptr() + 4 * self.SLOT * i
+
+    def _slot_view(self, i, numel):
+        return self.scratch[self.SLOT * i:self.SLOT * i + numel]
+
+    def _allreduce(self, t, kind):
+        from . import dataparallel
+        dataparallel.all_reduce_sum(t, kind)
+
+    def _gather_merge(self, local, n_sets, C, n_local, mean, invstd, var=None, kind="bn_fwd"):
+        """local [n_sets, 2, C] = per-rank (mean, M2) -> all_gather -> Chan merge (equal row counts) -> mean / invstd [/ var] [n_sets, C]"""
+        from . import dataparallel
+        W = self.world
+        gathered = torch.empty((W,) + tuple(local.shape), dtype=torch.float32, device=self.dev)
+        dataparallel.all_gather(gathered, local.contiguous(), kind)
+        _native.check(_L().dexgg_bn_merge(gathered.data_ptr(), W, n_sets, C, float(n_local), EPS, mean, invstd, var, _st(self.dev)))
 
     def _begin_step(self):
         self.scratch.zero_()
@@ -218,8 +246,9 @@ class TrainEngine:
         a.x, a.ldx, a.C, a.rows_per_group, a.n_groups = x, ldx, C, rpg, groups
         a.gamma, a.beta, a.shift = bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr()
         a.mean, a.invstd = stat[0].data_ptr(), stat[1].data_ptr()
-        a.acc, a.barrier = self._next_slot(), self.bar.data_ptr()
-        a.eps, a.count_total = EPS, float(rpg)
+        slot = self._next_slot()
+        a.acc, a.barrier = self._slot_ptr(slot), self.bar.data_ptr()
+        a.eps, a.count_total = EPS, float(rpg * self.world)
         a.residual, a.ldr, a.act = res, ldr, 1
         if drop is not None:
             mask, p, stream = drop
@@ -227,6 +256,11 @@ class TrainEngine:
                 a.drop_mask, a.ldm = mask.data_ptr(), mask.stride(0)
             a.drop_p, a.drop_seed, a.drop_stream = float(p), self.seed.data_ptr(), int(stream)
         a.y, a.ldy, a.mode = y, ldy, 0
+        if self.world > 1:  # local shifted sums -> ONE allreduce -> normalise with the global statistics
+            a.mode = 1
+            _native.check(_L().dexgg_bn_fwd_slab(ctypes.byref(a), _st(self.dev)))
+            self._allreduce(self._slot_view(slot, groups * 2 * C), "bn_fwd")
+            a.mode = 2
         _native.check(_L().dexgg_bn_fwd_slab(ctypes.byref(a), _st(self.dev)))
 
     def _bn_bwd(self, C, rpg, groups, bn, stat, x, ldx, out, ldo, gx, ldgx, g=None, ldg=0, rank1=None, skip=None, lds=0, gskip=None, ldgs=0,
@@ -245,7 +279,7 @@ class TrainEngine:
             a.drop_p, a.drop_seed, a.drop_stream = float(p), self.seed.data_ptr(), int(stream)
         a.x, a.ldx = x, ldx
         a.mean, a.invstd, a.gamma = stat[0].data_ptr(), stat[1].data_ptr(), bn.weight.data_ptr()
-        a.C, a.rows_per_group, a.n_groups, a.count_total = C, rpg, groups, float(rpg)
+        a.C, a.rows_per_group, a.n_groups, a.count_total = C, rpg, groups, float(rpg * self.world)
         if want_wgrad:
             a.dgamma, a.dbeta = bn.weight.grad.data_ptr(), bn.bias.grad.data_ptr()
         a.gx, a.ldgx = gx, ldgx
@@ -253,7 +287,13 @@ class TrainEngine:
             a.skip, a.lds, a.gskip, a.ldgs = skip, lds, gskip, ldgs
             a.dbias_skip = dbias_skip if want_wgrad else None
         a.mode = 0
-        a.acc, a.barrier = self._next_slot(), self.bar.data_ptr()
+        slot = self._next_slot()
+        a.acc, a.barrier = self._slot_ptr(slot), self.bar.data_ptr()
+        if self.world > 1:
+            a.mode = 1
+            _native.check(_L().dexgg_bn_bwd_slab(ctypes.byref(a), _st(self.dev)))
+            self._allreduce(self._slot_view(slot, groups * 2 * C), "bn_bwd")
+            a.mode = 2
         _native.check(_L().dexgg_bn_bwd_slab(ctypes.byref(a), _st(self.dev)))
 
     @staticmethod
@@ -285,8 +325,16 @@ class TrainEngine:
         if net.tail_bn:
             rm = net.in_bn.running_mean.data_ptr() + 4 * BPS
             rv = net.in_bn.running_var.data_ptr() + 4 * BPS
-        _native.check(_L().dexgg_tail_pack(ctypes.byref(src), rows, int(net.tail_bn), EPS, float(rows), float(net.in_bn.momentum or 0.1),
-                                           st[0].data_ptr(), st[1].data_ptr(), rm, rv, P, LD, C0, 0, None, _st(self.dev)))
+        args = (ctypes.byref(src), rows, int(net.tail_bn), EPS, float(rows * self.world), float(net.in_bn.momentum or 0.1),
+                st[0].data_ptr(), st[1].data_ptr(), rm, rv, P, LD, C0)
+        if self.world > 1 and net.tail_bn:
+            T = net.n_tail
+            slot = self._next_slot()
+            _native.check(_L().dexgg_tail_pack(*args, 1, self._slot_ptr(slot), _st(self.dev)))
+            self._gather_merge(self._slot_view(slot, 2 * T).view(1, 2, T), 1, T, rows, st[0].data_ptr(), st[1].data_ptr())
+            _native.check(_L().dexgg_tail_pack(*args, 2, None, _st(self.dev)))
+        else:
+            _native.check(_L().dexgg_tail_pack(*args, 0, None, _st(self.dev)))
 
     # ------------------------------------------------------------------------------------------------ weights
     def _weight_jobs(self, net, grads):
@@ -368,7 +416,7 @@ class TrainEngine:
             e.running_mean, e.running_var, e.mean, e.second = bn.running_mean.data_ptr(), bn.running_var.data_ptr(), mean, second
             e.num_batches_tracked = bn.num_batches_tracked.data_ptr() if nbt else None
             e.C, e.n_groups, e.second_is_var, e.same_row = C, groups, int(is_var), int(same_row)
-            e.count, e.eps, e.momentum = float(rpg), EPS, float(bn.momentum or 0.1)
+            e.count, e.eps, e.momentum = float(rpg * self.world), EPS, float(bn.momentum or 0.1)
             n += 1
         put(net.in_bn, self.bps_stat[0].data_ptr(), self.bps_stat[1].data_ptr(), BPS, True, True)
         for b, blk in enumerate(net.blocks):
@@ -381,7 +429,7 @@ class TrainEngine:
         rpg = R // groups
         nb = len(net.blocks)
         if want_wgrad:
-            net.db13.zero_()
+            net.small_scratch.zero_()  # db13 of every block + the dWxt scratch of every block (split contractions accumulate)
         g_src = last
         for b in range(nb - 1, -1, -1):
             blk, rb = net.blocks[b], net.blocks[b].rb
@@ -399,7 +447,8 @@ class TrainEngine:
             xin, ldx, K2 = self._block_in(net, b)
             if want_wgrad:  # gradients wrt the folded first-layer weights: [768, 4096] and [768, X | tail]
                 self._gemm(NCAT, BPS, [(net.G13.data_ptr(), NCAT, 1, xhat.data_ptr(), BPS, 1, R)], C32=blk.dWb, ldc=BPS)
-                self._gemm(NCAT, blk.ldxt, [(net.G13.data_ptr(), NCAT, 1, xin.data_ptr(), ldx, 1, R)], C32=blk.dWxt, ldc=blk.ldxt)
+                self._gemm(NCAT, blk.ldxt, [(net.G13.data_ptr(), NCAT, 1, xin.data_ptr(), ldx, 1, R)], C32=blk.dWxt, ldc=blk.ldxt,
+                           split_k=max(1, min(4 if blk.has_x else 16, R // 512)))
             if b > 0 or want_tail_grad:
                 self._gemm(R, blk.ldxt, [(net.G13.data_ptr(), NCAT, 0, blk.Wxt.data_ptr(), blk.ldxt, 1, NCAT)], C16=net.gXT[b], ldc=blk.ldxt)
                 g_src = ("mat", net.gXT[b], blk.ldxt)
@@ -422,8 +471,12 @@ class TrainEngine:
         B = self.B
         assert bps.shape == (B, BPS) and bps.dtype == torch.float32 and bps.is_contiguous() and bps.is_cuda
         s = self.bps_stat
+        slot = self._next_slot(2)  # [2, 4096] floats = two slots
         _native.check(_L().dexgg_bn_input_stats(bps.data_ptr(), BPS, B, BPS, EPS, s[0].data_ptr(), s[1].data_ptr(), s[2].data_ptr(),
-                                                self._next_slot() + 0 * self._next_slot(), _st(self.dev)))  # [2, 4096] floats = two slots
+                                                self._slot_ptr(slot), _st(self.dev)))
+        if self.world > 1:  # per-rank (mean, M2 = B * var) -> all_gather -> Chan merge
+            local = torch.stack([s[0], s[1] * float(B)]).view(1, 2, BPS)
+            self._gather_merge(local, 1, BPS, B, s[0].data_ptr(), s[2].data_ptr(), s[1].data_ptr())
         _native.check(_L().dexgg_xhat(bps.data_ptr(), BPS, s[0].data_ptr(), s[2].data_ptr(), B, BPS, self.xhat.data_ptr(), 2, _st(self.dev)))
 
     def _dev_batch(self, data, keys):
@@ -480,8 +533,15 @@ class TrainEngine:
                 self.backward_blocks(D, B, 1, self.xhat, ("rank1", D.dl, D.head.weight, None), False, True)
                 src = self._tail_src(fake_tail)
                 st = D.tail_stat[0]
-                _native.check(_L().dexgg_tail_bn_bwd(ctypes.byref(src), B, float(B), st[0].data_ptr(), st[1].data_ptr(), D.gXT[0].data_ptr(), TAILW, 0,
-                                                     D.gXT[1].data_ptr(), LDXT, HID, self.gPose.data_ptr(), 0, None, _st(dev)))
+                targs = (ctypes.byref(src), B, float(B * self.world), st[0].data_ptr(), st[1].data_ptr(), D.gXT[0].data_ptr(), TAILW, 0,
+                         D.gXT[1].data_ptr(), LDXT, HID, self.gPose.data_ptr())
+                if self.world > 1:
+                    slot = self._next_slot()
+                    _native.check(_L().dexgg_tail_bn_bwd(*targs, 1, self._slot_ptr(slot), _st(dev)))
+                    self._allreduce(self._slot_view(slot, 2 * D.n_tail), "bn_bwd")
+                    _native.check(_L().dexgg_tail_bn_bwd(*targs, 2, self._slot_ptr(slot), _st(dev)))
+                else:
+                    _native.check(_L().dexgg_tail_bn_bwd(*targs, 0, None, _st(dev)))
                 G.flat_grad.zero_()
                 self.dWh.zero_()
                 self.dbh.zero_()
@@ -495,6 +555,9 @@ class TrainEngine:
                 self.unfold(G)
                 m._sync_grads(G.module)
                 G.optimizer.step()
+            if self.world > 1:  # report the global-batch means
+                self._allreduce(self.loss, "grad")
+                self.loss.div_(self.world)
             vals = self.mix @ self.loss
         out = {"total_loss_disc": vals[0], "bce_loss_real": vals[1], "bce_loss_fake": vals[2]}
         if is_train_gen:
@@ -533,6 +596,9 @@ class TrainEngine:
             m._sync_grads(E.module)
             E.optimizer.step()
             val = self.loss[6].clone()
+            if self.world > 1:
+                self._allreduce(val, "grad")
+                val.div_(self.world)
         self._bump_versions(self.E)
         return {"total_loss_eva": val, "bce_loss": val}
 

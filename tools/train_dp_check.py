@@ -63,6 +63,16 @@ for k in sd_a:
     d = float((sd_a[k].double() - sd_b[k].double()).abs().max())
     key = "max_weight_diff" if k in params else "max_buffer_diff"
     out[key] = max(out[key], d)
+# gradients left by the step: the averaged sharded gradients must equal the full-batch gradients (relative L2 norm, worst tensor)
+ga, gb = dict(ref.DexGANGrasp.named_parameters()), dict(dp.DexGANGrasp.named_parameters())
+worst = (0.0, "")
+for k in ga:
+    if ga[k].grad is None or gb[k].grad is None or k.endswith(("fc1.bias", "fc2.bias")):
+        continue
+    den = float(ga[k].grad.double().norm())
+    if den > 1e-9:
+        worst = max(worst, (float((ga[k].grad.double() - gb[k].grad.double()).norm()) / den, k))
+out["worst_grad_rel_diff"] = worst
 # weights must be identical on every rank after the step
 flat = torch.cat([p.detach().reshape(-1) for p in dp.DexGANGrasp.parameters()])
 mx, mn = flat.clone(), flat.clone()
