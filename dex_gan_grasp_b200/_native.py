@@ -60,6 +60,12 @@ SIGNATURES = {
     "dexgg_bn_running_multi": (c_int, [c_void_p, c_int, c_void_p]),
     "dexgg_bn_merge": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "dexgg_bump_counter": (c_int, [c_void_p, c_void_p]),
+    "dexgg_slab_scratch_bytes": (c_size_t, []),
+    "dexgg_peer_alloc": (c_int, [c_size_t, ctypes.POINTER(c_void_p), c_void_p]),
+    "dexgg_peer_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "dexgg_peer_close": (c_int, [c_void_p]),
+    "dexgg_peer_free": (c_int, [c_void_p]),
+    "dexgg_slab_step_begin": (c_int, [c_void_p, c_void_p, c_void_p]),
     "dexgg_f32_to_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_f32_to_bf16_t": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_rot6d_forward": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
@@ -100,12 +106,17 @@ class Gemm(ctypes.Structure):
 c_uint, c_ull = ctypes.c_uint, ctypes.c_ulonglong
 
 
+class SlabComm(ctypes.Structure):
+    """include/dexgg.h: dexgg_slab_comm"""
+    _fields_ = [("peers", c_void_p), ("world", c_int), ("rank", c_int), ("slot", c_int), ("parity", c_void_p)]
+
+
 class BnFwd(ctypes.Structure):
     """include/dexgg.h: dexgg_bn_fwd"""
     _fields_ = [("x", c_void_p), ("ldx", c_int64), ("C", c_int), ("rows_per_group", c_int64), ("n_groups", c_int), ("gamma", c_void_p),
                 ("beta", c_void_p), ("shift", c_void_p), ("mean", c_void_p), ("invstd", c_void_p), ("eps", c_float), ("count_total", c_float),
                 ("residual", c_void_p), ("ldr", c_int64), ("act", c_int), ("drop_mask", c_void_p), ("ldm", c_int64), ("drop_p", c_float),
-                ("drop_seed", c_void_p), ("drop_stream", c_uint), ("y", c_void_p), ("ldy", c_int64), ("mode", c_int), ("acc", c_void_p), ("barrier", c_void_p)]
+                ("drop_seed", c_void_p), ("drop_stream", c_uint), ("y", c_void_p), ("ldy", c_int64), ("mode", c_int), ("acc", c_void_p), ("comm", SlabComm)]
 
 
 class BnBwd(ctypes.Structure):
@@ -115,7 +126,7 @@ class BnBwd(ctypes.Structure):
                 ("drop_stream", c_uint), ("x", c_void_p), ("ldx", c_int64), ("mean", c_void_p), ("invstd", c_void_p), ("gamma", c_void_p),
                 ("C", c_int), ("rows_per_group", c_int64), ("n_groups", c_int), ("count_total", c_float), ("dgamma", c_void_p),
                 ("dbeta", c_void_p), ("gx", c_void_p), ("ldgx", c_int64), ("skip", c_void_p), ("lds", c_int64), ("gskip", c_void_p),
-                ("ldgs", c_int64), ("dbias_skip", c_void_p), ("mode", c_int), ("acc", c_void_p), ("barrier", c_void_p)]
+                ("ldgs", c_int64), ("dbias_skip", c_void_p), ("mode", c_int), ("acc", c_void_p), ("comm", SlabComm)]
 
 
 class TailSrc(ctypes.Structure):

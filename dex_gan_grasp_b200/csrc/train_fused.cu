@@ -20,6 +20,8 @@
 #include "common.cuh"
 #include "pose.cuh"
 
+#include <string.h>
+
 namespace dexgg {
 
 constexpr float TF_SLOPE = 0.2f;
@@ -90,25 +92,75 @@ __device__ __forceinline__ void slab_reduce(float (&acc)[NQ][8], float* sm /* [8
         for (int j = 0; j < 8; ++j) acc[q][j] = out[(sub * NQ + q) * 8 + j];
 }
 
-// Barrier over all CTAs of a slab kernel.  The grids are sized to at most one CTA per SM (128 - 148 CTAs of 256 threads, a few
-// KB of shared memory), launched stream-ordered behind their producer, so every CTA is resident when the first one arrives.
-// bar[0] = arrival counter (reset by the last arriver), bar[1] = generation.
-__device__ __forceinline__ void slab_grid_barrier(unsigned* bar, unsigned nblocks) {
+// ---- column sums across the CTAs of a slab kernel AND across the GPUs of a data-parallel job, inside the kernel ----
+// Every rank owns a peer-mapped scratch (cudaIpc, NVLink P2P): two parity buffers of SLAB_SLOTS slots; a slab launch uses one
+// slot: [local accumulator 2048 f | one 2048-float slice per rank | counters].  Protocol of a launch (every rank runs the same
+// launch sequence, so slot numbers and grid sizes agree):
+//   1. each CTA adds its partial column sums to the LOCAL accumulator (atomics) and bumps the local arrival counter;
+//   2. the last CTA to arrive copies the local totals into slice[rank] of EVERY rank's slot (plain stores over NVLink, a
+//      system-scope fence) and then bumps every rank's `published` counter;
+//   3. every CTA spins until its own rank's `published` == world, then sums the slices in rank order: all ranks get bit-identical
+//      totals, with ONE exchange per BatchNorm and no NCCL launch.  world == 1 is the same code (one slice).
+// The grids hold at most one CTA per SM and run stream-ordered behind their producers, so every CTA is resident while it spins.
+// The parity buffer alternates per step (dexgg_slab_step_begin flips it on the device and zeroes the other one for the next
+// step), which keeps a fast rank's next-step traffic out of a slow rank's current-step slots.
+constexpr int SLAB_ACC = 2048, SLAB_MAXW = 8, SLAB_SLOT_FLOATS = SLAB_ACC * (1 + SLAB_MAXW) + 64, SLAB_SLOTS = 32;
+struct SlabComm {
+    float* const* peers;       // device array [world]: scratch base of every rank (peers[rank] = own)
+    int world, rank, slot;
+    const unsigned* parity;    // device word, 0 / 1
+};
+__device__ __forceinline__ float* slab_slot(const SlabComm& c, int peer) {
+    return c.peers[peer] + ((size_t)(*c.parity) * SLAB_SLOTS + c.slot) * SLAB_SLOT_FLOATS;
+}
+// n floats of the local accumulator are exchanged; returns (in every thread) a pointer to this rank's slot
+__device__ __forceinline__ float* slab_exchange(const SlabComm& c, int n, unsigned nblocks) {
+    __shared__ int s_last;
+    float* mine = slab_slot(c, c.rank);
+    unsigned* cnt = reinterpret_cast<unsigned*>(mine + SLAB_ACC * (1 + SLAB_MAXW));
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
-        const unsigned gen = *reinterpret_cast<volatile unsigned*>(bar + 1);
-        if (atomicAdd(bar, 1u) == nblocks - 1) {
-            *reinterpret_cast<volatile unsigned*>(bar) = 0u;
-            __threadfence();
-            atomicAdd(bar + 1, 1u);
-        } else {
-            while (*reinterpret_cast<volatile unsigned*>(bar + 1) == gen) __nanosleep(40);
-        }
-        __threadfence();
+        s_last = atomicAdd(cnt, 1u) == nblocks - 1;
     }
     __syncthreads();
+    if (s_last) {
+        __threadfence();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const float v = __ldcg(mine + i);
+            for (int p = 0; p < c.world; ++p) __stcg(slab_slot(c, p) + SLAB_ACC * (1 + c.rank) + i, v);
+        }
+        __threadfence_system();
+        __syncthreads();
+        if ((int)threadIdx.x < c.world)
+            atomicAdd_system(reinterpret_cast<unsigned*>(slab_slot(c, threadIdx.x) + SLAB_ACC * (1 + SLAB_MAXW)) + 1, 1u);
+    }
+    if (threadIdx.x == 0) {
+        volatile unsigned* pub = cnt + 1;
+        while (*pub < (unsigned)c.world) __nanosleep(40);
+        __threadfence_system();
+    }
+    __syncthreads();
+    return mine;
 }
+__device__ __forceinline__ float slab_total(const SlabComm& c, const float* mine, int i) {
+    float t = 0.f;
+    for (int r = 0; r < c.world; ++r) t += __ldcv(mine + SLAB_ACC * (1 + r) + i);
+    return t;
+}
+// flips the step parity and zeroes the OTHER parity buffer (used by the next step)
+__global__ void slab_step_begin_kernel(float* base, unsigned* parity) {
+    __shared__ unsigned s_p;
+    if (threadIdx.x == 0) {
+        if (blockIdx.x == 0) s_p = *parity ^ 1u;   // block 0 flips; the other blocks compute the same value without writing
+        else s_p = *parity ^ 1u;
+    }
+    __syncthreads();
+    float* other = base + (size_t)(s_p ^ 1u) * SLAB_SLOTS * SLAB_SLOT_FLOATS;
+    const size_t n = (size_t)SLAB_SLOTS * SLAB_SLOT_FLOATS;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) other[i] = 0.f;
+}
+__global__ void slab_parity_flip_kernel(unsigned* parity) { *parity ^= 1u; }
 
 // ------------------------------------------------------------------------------------------------ BatchNorm forward slab
 // grid (C / 16 column slabs, row splits, n_groups): a CTA owns 16 columns x one row range of one batch group.  Pass 1 adds the
@@ -124,9 +176,9 @@ struct BnFwd {
     int act;
     const float* mask; int64_t ldm; float drop_p; const unsigned long long* seed; unsigned stream;
     __nv_bfloat16* y; int64_t ldy;
-    int mode;                      // 0 fused, 1 partial sums only (data parallel: allreduce acc, then mode 2), 2 apply from acc
-    float* acc;                    // [n_groups, 2, C] zeroed by the caller
-    unsigned* bar;
+    int mode;                      // 0 fused (in-kernel exchange), 1 partial sums only (NCCL fallback: allreduce acc, then mode 2), 2 apply from acc
+    float* acc;                    // modes 1 / 2: [n_groups, 2, C] zeroed by the caller
+    SlabComm comm;                 // mode 0
 };
 
 __global__ void __launch_bounds__(256) bn_fwd_slab_kernel(const BnFwd a) {
@@ -139,7 +191,8 @@ __global__ void __launch_bounds__(256) bn_fwd_slab_kernel(const BnFwd a) {
     float s[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) s[j] = a.shift ? a.shift[c0 + j] : 0.f;
-    float* accg = a.acc + (int64_t)g * 2 * a.C;
+    float* accl = a.mode == 0 ? slab_slot(a.comm, a.comm.rank) : a.acc;  // local accumulator [n_groups, 2, C]
+    float* accg = accl + (int64_t)g * 2 * a.C;
     if (a.mode != 2) {
         float acc[2][8];
 #pragma unroll
@@ -164,12 +217,14 @@ __global__ void __launch_bounds__(256) bn_fwd_slab_kernel(const BnFwd a) {
             }
         }
         if (a.mode == 1) return;
-        slab_grid_barrier(a.bar, gridDim.x * gridDim.y * gridDim.z);
+        slab_exchange(a.comm, a.n_groups * 2 * a.C, gridDim.x * gridDim.y * gridDim.z);
     }
     float sc[8], sh[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float sd = __ldcg(accg + c0 + j), sq = __ldcg(accg + a.C + c0 + j);
+        const int i0 = g * 2 * a.C + c0 + j;
+        const float sd = a.mode == 0 ? slab_total(a.comm, accl, i0) : __ldcg(accg + c0 + j);
+        const float sq = a.mode == 0 ? slab_total(a.comm, accl, i0 + a.C) : __ldcg(accg + a.C + c0 + j);
         const float mean = s[j] + sd / a.count;
         const float var = fmaxf(sq / a.count - (sd / a.count) * (sd / a.count), 0.f);
         const float istd = rsqrtf(var + a.eps);
@@ -224,9 +279,9 @@ struct BnBwd {
     const __nv_bfloat16* skip; int64_t lds;     // skip-branch activation (post-LeakyReLU) or NULL
     __nv_bfloat16* gskip; int64_t ldgs;         // out: g * LeakyReLU'(skip)
     float* dbias_skip;                          // [C] += sum_m gskip (may be NULL)
-    int mode;                                   // 0 fused, 1 column sums only (data parallel: allreduce acc, then mode 2), 2 apply from acc
-    float* acc;                                 // [n_groups, 2, C] zeroed by the caller: sum g, sum g * xhat
-    unsigned* bar;
+    int mode;                                   // 0 fused (in-kernel exchange), 1 column sums only (NCCL fallback), 2 apply from acc
+    float* acc;                                 // modes 1 / 2: [n_groups, 2, C] zeroed by the caller: sum g, sum g * xhat
+    SlabComm comm;                              // mode 0
 };
 
 __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
@@ -268,7 +323,8 @@ __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
             }
         }
     };
-    float* accg = a.acc + (int64_t)gi * 2 * a.C;
+    float* accl = a.mode == 0 ? slab_slot(a.comm, a.comm.rank) : a.acc;
+    float* accg = accl + (int64_t)gi * 2 * a.C;
     if (a.mode != 2) {
         float S[4][8];  // 0: sum g, 1: sum g * xhat, 2: sum dl * out, 3: sum gskip
 #pragma unroll
@@ -310,14 +366,15 @@ __global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
             }
         }
         if (a.mode == 1) return;
-        slab_grid_barrier(a.bar, gridDim.x * gridDim.y * gridDim.z);
+        slab_exchange(a.comm, a.n_groups * 2 * a.C, gridDim.x * gridDim.y * gridDim.z);
     }
     float k0[8], k1[8], k2[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
+        const int i0 = gi * 2 * a.C + c0 + j;
         k0[j] = a.gamma[c0 + j] * istd[j];
-        k1[j] = __ldcg(accg + c0 + j) / a.count;
-        k2[j] = __ldcg(accg + a.C + c0 + j) / a.count;
+        k1[j] = (a.mode == 0 ? slab_total(a.comm, accl, i0) : __ldcg(accg + c0 + j)) / a.count;
+        k2[j] = (a.mode == 0 ? slab_total(a.comm, accl, i0 + a.C) : __ldcg(accg + a.C + c0 + j)) / a.count;
     }
 #pragma unroll 2
     for (int64_t r = r0 + rl; r < r1; r += 128) {
@@ -883,6 +940,17 @@ using namespace dexgg;
 
 #define TF_ST static_cast<cudaStream_t>(stream)
 
+static int slab_comm(const dexgg_slab_comm& q, int mode, const float* acc, int n, SlabComm& c) {
+    c.peers = reinterpret_cast<float* const*>(q.peers); c.world = q.world; c.rank = q.rank; c.slot = q.slot; c.parity = q.parity;
+    if (mode == 0) {
+        DEXGG_REQUIRE(q.peers && q.parity && q.world >= 1 && q.world <= SLAB_MAXW && q.rank >= 0 && q.rank < q.world && q.slot >= 0 &&
+                      q.slot < SLAB_SLOTS && n <= SLAB_ACC, "slab kernel: bad exchange descriptor (world %d rank %d slot %d n %d)", q.world, q.rank, q.slot, n);
+    } else {
+        DEXGG_REQUIRE(acc, "slab kernel: accumulator scratch missing");
+    }
+    return DEXGG_OK;
+}
+
 // (column slabs, row splits, groups) with at most one CTA per SM in total: the kernels synchronise the grid with a barrier
 static dim3 slab_grid(int C, int64_t rows_per_group, int n_groups) {
     const int slabs = C / 16;
@@ -905,8 +973,8 @@ extern "C" int dexgg_bn_fwd_slab(const dexgg_bn_fwd* q, void* stream) {
     a.count = q->count_total > 0.f ? q->count_total : (float)q->rows_per_group;
     a.res = static_cast<const __nv_bfloat16*>(q->residual); a.ldr = q->ldr; a.act = q->act;
     a.mask = q->drop_mask; a.ldm = q->ldm; a.drop_p = q->drop_p; a.seed = q->drop_seed; a.stream = q->drop_stream;
-    a.y = static_cast<__nv_bfloat16*>(q->y); a.ldy = q->ldy; a.mode = q->mode; a.acc = q->acc; a.bar = q->barrier;
-    DEXGG_REQUIRE(a.acc && (q->mode != 0 || a.bar), "bn_fwd_slab: accumulator / barrier scratch missing");
+    a.y = static_cast<__nv_bfloat16*>(q->y); a.ldy = q->ldy; a.mode = q->mode; a.acc = q->acc;
+    if (int rc = slab_comm(q->comm, q->mode, q->acc, q->n_groups * 2 * q->C, a.comm)) return rc;
     bn_fwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_fwd_slab_kernel");
@@ -928,8 +996,8 @@ extern "C" int dexgg_bn_bwd_slab(const dexgg_bn_bwd* q, void* stream) {
     a.count = q->count_total > 0.f ? q->count_total : (float)q->rows_per_group;
     a.dgamma = q->dgamma; a.dbeta = q->dbeta; a.gx = static_cast<__nv_bfloat16*>(q->gx); a.ldgx = q->ldgx;
     a.skip = static_cast<const __nv_bfloat16*>(q->skip); a.lds = q->lds; a.gskip = static_cast<__nv_bfloat16*>(q->gskip); a.ldgs = q->ldgs;
-    a.dbias_skip = q->dbias_skip; a.mode = q->mode; a.acc = q->acc; a.bar = q->barrier;
-    DEXGG_REQUIRE(a.acc && (q->mode != 0 || a.bar), "bn_bwd_slab: accumulator / barrier scratch missing");
+    a.dbias_skip = q->dbias_skip; a.mode = q->mode; a.acc = q->acc;
+    if (int rc = slab_comm(q->comm, q->mode, q->acc, q->n_groups * 2 * q->C, a.comm)) return rc;
     bn_bwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_bwd_slab_kernel");
@@ -1118,5 +1186,46 @@ extern "C" int dexgg_bump_counter(unsigned long long* counter, void* stream) {
     bump_counter_kernel<<<1, 1, 0, TF_ST>>>(counter);
     count_launches(1);
     DEXGG_LAUNCH_OK("bump_counter_kernel");
+    return DEXGG_OK;
+}
+
+// ---- peer-mapped scratch of the in-kernel exchange (one per rank; handles travel through torch.distributed) ----
+extern "C" size_t dexgg_slab_scratch_bytes(void) { return (size_t)2 * SLAB_SLOTS * SLAB_SLOT_FLOATS * sizeof(float); }
+
+extern "C" int dexgg_peer_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(ptr && handle64 && bytes > 0, "peer_alloc: bad arguments");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    DEXGG_CUDA_OK(cudaMalloc(ptr, bytes));
+    DEXGG_CUDA_OK(cudaMemset(*ptr, 0, bytes));
+    cudaIpcMemHandle_t h;
+    DEXGG_CUDA_OK(cudaIpcGetMemHandle(&h, *ptr));
+    memcpy(handle64, &h, 64);
+    return DEXGG_OK;
+}
+extern "C" int dexgg_peer_open(const unsigned char* handle64, void** ptr) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(ptr && handle64, "peer_open: bad arguments");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    DEXGG_CUDA_OK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return DEXGG_OK;
+}
+extern "C" int dexgg_peer_close(void* ptr) {
+    if (ptr) DEXGG_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+    return DEXGG_OK;
+}
+extern "C" int dexgg_peer_free(void* ptr) {
+    if (ptr) DEXGG_CUDA_OK(cudaFree(ptr));
+    return DEXGG_OK;
+}
+// start of a training step: flip the parity word, zero the other parity buffer for the next step
+extern "C" int dexgg_slab_step_begin(void* scratch_base, unsigned* parity, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(scratch_base && parity, "slab_step_begin: null");
+    slab_step_begin_kernel<<<64, 256, 0, TF_ST>>>(static_cast<float*>(scratch_base), parity);
+    slab_parity_flip_kernel<<<1, 1, 0, TF_ST>>>(parity);
+    count_launches(2);
+    DEXGG_LAUNCH_OK("slab_step_begin kernels");
     return DEXGG_OK;
 }

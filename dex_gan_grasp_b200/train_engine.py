@@ -22,6 +22,8 @@ import torch
 import torch.distributed as dist
 
 from . import _native
+import os
+
 from ._native import BnBwd, BnFwd, FirstLayer, Gemm, PlainJob, RunEntry, ScoreHead, TailSrc, WeightJobs
 
 BPS, HID, INNER, NCAT = 4096, 512, 256, 768
@@ -194,9 +196,49 @@ class TrainEngine:
         # at the start of a step and every launch of the step takes the next slot) + the words of their grid barrier
         self.SLOT = 4096
         self.world = _world()
+        self.rank = dist.get_rank() if self.world > 1 else 0
+        self._setup_exchange()
         self.scratch = torch.zeros((64 * self.SLOT,), **f32)
         self.bar = torch.zeros((4,), dtype=torch.int32, device=dev)
         self._slot = 0
+
+    def _setup_exchange(self):
+        """Peer-mapped scratch of the slab kernels' in-kernel exchange (csrc/train_fused.cu: slab_exchange): every rank allocates
+        one, the cudaIpc handles travel through torch.distributed, every rank maps the others'.  DEXGG_DP_EXCHANGE=nccl keeps the
+        NCCL fallback (one allreduce per BatchNorm between a sums-only and an apply launch)."""
+        L = _L()
+        self.p2p = (os.environ.get("DEXGG_DP_EXCHANGE", "p2p") != "nccl" and self.world <= 8) or self.world == 1
+        self._pslot = 0
+        if not self.p2p:
+            return
+        with torch.cuda.device(self.dev):
+            nbytes = L.dexgg_slab_scratch_bytes()
+            mine, handle = ctypes.c_void_p(), (ctypes.c_ubyte * 64)()
+            _native.check(L.dexgg_peer_alloc(nbytes, ctypes.byref(mine), handle))
+            self._peer_mine, self._peer_opened = mine, []
+            ptrs = [mine.value]
+            if self.world > 1:
+                handles = [None] * self.world
+                dist.all_gather_object(handles, bytes(handle))
+                ptrs = []
+                for r, h in enumerate(handles):
+                    if r == self.rank:
+                        ptrs.append(mine.value)
+                        continue
+                    q = ctypes.c_void_p()
+                    _native.check(L.dexgg_peer_open((ctypes.c_ubyte * 64).from_buffer_copy(h), ctypes.byref(q)))
+                    self._peer_opened.append(q)
+                    ptrs.append(q.value)
+            self.peer_table = torch.tensor(ptrs, dtype=torch.int64, device=self.dev)
+            self.parity = torch.zeros((1,), dtype=torch.int32, device=self.dev)
+            if self.world > 1:
+                dist.barrier()  # every rank has mapped every scratch before anyone launches into it
+
+    def _comm(self, a):
+        c = a.comm
+        c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
+        self._pslot += 1
+        assert self._pslot <= 32
 
     def _next_slot(self, n=1):
         """index of the next `n` free accumulator slots of this step"""
@@ -226,6 +268,9 @@ class TrainEngine:
     def _begin_step(self):
         self.scratch.zero_()
         self._slot = 0
+        if self.p2p:
+            self._pslot = 0
+            _native.check(_L().dexgg_slab_step_begin(self._peer_mine, self.parity.data_ptr(), _st(self.dev)))
 
     # ------------------------------------------------------------------------------------------------ kernel wrappers
     def _gemm(self, M, N, segs, bias=None, act_from=None, C16=None, C32=None, ldc=None, split_k=0, accumulate=0):
@@ -247,7 +292,7 @@ class TrainEngine:
         a.gamma, a.beta, a.shift = bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr()
         a.mean, a.invstd = stat[0].data_ptr(), stat[1].data_ptr()
         slot = self._next_slot()
-        a.acc, a.barrier = self._slot_ptr(slot), self.bar.data_ptr()
+        a.acc = self._slot_ptr(slot)
         a.eps, a.count_total = EPS, float(rpg * self.world)
         a.residual, a.ldr, a.act = res, ldr, 1
         if drop is not None:
@@ -256,7 +301,9 @@ class TrainEngine:
                 a.drop_mask, a.ldm = mask.data_ptr(), mask.stride(0)
             a.drop_p, a.drop_seed, a.drop_stream = float(p), self.seed.data_ptr(), int(stream)
         a.y, a.ldy, a.mode = y, ldy, 0
-        if self.world > 1:  # local shifted sums -> ONE allreduce -> normalise with the global statistics
+        if self.p2p:
+            self._comm(a)
+        elif self.world > 1:  # NCCL fallback: local shifted sums -> ONE allreduce -> normalise with the global statistics
             a.mode = 1
             _native.check(_L().dexgg_bn_fwd_slab(ctypes.byref(a), _st(self.dev)))
             self._allreduce(self._slot_view(slot, groups * 2 * C), "bn_fwd")
@@ -288,8 +335,10 @@ class TrainEngine:
             a.dbias_skip = dbias_skip if want_wgrad else None
         a.mode = 0
         slot = self._next_slot()
-        a.acc, a.barrier = self._slot_ptr(slot), self.bar.data_ptr()
-        if self.world > 1:
+        a.acc = self._slot_ptr(slot)
+        if self.p2p:
+            self._comm(a)
+        elif self.world > 1:
             a.mode = 1
             _native.check(_L().dexgg_bn_bwd_slab(ctypes.byref(a), _st(self.dev)))
             self._allreduce(self._slot_view(slot, groups * 2 * C), "bn_bwd")

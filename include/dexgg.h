@@ -210,11 +210,29 @@ int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream);
  * (models/dexgangrasp.py:739-823; networks.py:43-56, 88-103, 148-159, 315-337; losses.py:61-76).  All matrices bf16 unless noted,
  * row pitches (ld, elements) multiples of 8; statistics, losses and parameter gradients fp32.
  * ---------------------------------------------------------------------------------------------------------- */
+/* Exchange descriptor of the slab kernels (mode 0): the column sums are combined across the CTAs of the launch AND across the
+ * ranks of a data-parallel job INSIDE the kernel, through peer-mapped scratch buffers (cudaIpc over NVLink) - one exchange per
+ * BatchNorm, no NCCL launch, bit-identical totals on every rank.  peers: DEVICE array [world] of every rank's scratch base
+ * (dexgg_peer_alloc(dexgg_slab_scratch_bytes()) on each rank, handles exchanged by the host, dexgg_peer_open on the others);
+ * slot: index of this launch inside the step (same on every rank, < 32); parity: device word flipped by dexgg_slab_step_begin
+ * at the start of every step.  world = 1: peers = {own scratch}. */
+typedef struct {
+    void* const* peers;
+    int world, rank, slot;
+    const unsigned* parity;
+} dexgg_slab_comm;
+size_t dexgg_slab_scratch_bytes(void);
+int dexgg_peer_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int dexgg_peer_open(const unsigned char* handle64, void** ptr);
+int dexgg_peer_close(void* ptr);
+int dexgg_peer_free(void* ptr);
+int dexgg_slab_step_begin(void* scratch_base, unsigned* parity, void* stream);
+
 /* Train-mode BatchNorm1d forward as ONE kernel: batch statistics of x per group of rows_per_group rows (the discriminator's
  * real and fake batches are two groups of one call), y = [dropout] LeakyReLU(gamma * xhat + beta [+ residual]).  A CTA owns
- * 16 columns x a row range; the grid (at most one CTA per SM) meets at a barrier between the statistics pass and the apply
- * pass.  mode 0: fused.  Data parallel: mode 1 adds the local shifted sums to acc and returns; after ONE allreduce of acc,
- * mode 2 applies (count_total = rows of a group over all ranks).  Dropout: drop_mask (fp32, pre-scaled keep mask) or, if NULL and
+ * 16 columns x a row range; the grid (at most one CTA per SM) exchanges its column sums between the statistics pass and the
+ * apply pass (mode 0: in-kernel, across CTAs and ranks - dexgg_slab_comm).  NCCL fallback: mode 1 adds the local shifted sums to
+ * acc and returns; after ONE allreduce of acc, mode 2 applies (count_total = rows of a group over all ranks).  Dropout: drop_mask (fp32, pre-scaled keep mask) or, if NULL and
  * drop_p > 0, a counter-based Bernoulli mask from *drop_seed and drop_stream (the backward regenerates it). */
 typedef struct {
     const void* x; int64_t ldx;
@@ -228,8 +246,8 @@ typedef struct {
     const float* drop_mask; int64_t ldm; float drop_p; const unsigned long long* drop_seed; unsigned drop_stream;
     void* y; int64_t ldy;
     int mode;
-    float* acc;                          /* [n_groups, 2, C] scratch, ZEROED by the caller: shifted column sums */
-    unsigned* barrier;                   /* [2] grid-barrier words (mode 0), zero-initialised once */
+    float* acc;                          /* modes 1 / 2 (NCCL fallback): [n_groups, 2, C] scratch, ZEROED by the caller */
+    dexgg_slab_comm comm;                /* mode 0 */
 } dexgg_bn_fwd;
 int dexgg_bn_fwd_slab(const dexgg_bn_fwd* args, void* stream);
 
@@ -248,8 +266,8 @@ typedef struct {
     void* gx; int64_t ldgx;
     const void* skip; int64_t lds; void* gskip; int64_t ldgs; float* dbias_skip;
     int mode;                            /* data parallel: 1 = local column sums into acc; 2 = apply with the (allreduced) acc */
-    float* acc;                          /* [n_groups, 2, C] scratch, ZEROED by the caller */
-    unsigned* barrier;
+    float* acc;                          /* modes 1 / 2: [n_groups, 2, C] scratch, ZEROED by the caller */
+    dexgg_slab_comm comm;                /* mode 0 */
 } dexgg_bn_bwd;
 int dexgg_bn_bwd_slab(const dexgg_bn_bwd* args, void* stream);
 
