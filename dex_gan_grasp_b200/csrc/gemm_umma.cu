@@ -272,7 +272,7 @@ extern "C" int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream) {
     else {  // fewest waves of (128 + BN)-wide operand traffic: the big-K layers are bound by L2 -> SM bytes per tile, not MMA issue
         const int64_t mt = (g->M + GM_BM - 1) / GM_BM;
         int64_t best = -1;
-        for (int bn : {256, 192, 128}) {
+        for (int bn : {256, 192, 128, 64}) {
             const int64_t tiles = mt * ((g->N + bn - 1) / bn) * split;
             const int64_t cost = ((tiles + sm_count() - 1) / sm_count()) * (128 + bn);
             if (best < 0 || cost < best) { best = cost; BN = bn; }

@@ -104,7 +104,7 @@ __device__ __forceinline__ void slab_reduce(float (&acc)[NQ][8], float* sm /* [8
 // The grids hold at most one CTA per SM and run stream-ordered behind their producers, so every CTA is resident while it spins.
 // The parity buffer alternates per step (dexgg_slab_step_begin flips it on the device and zeroes the other one for the next
 // step), which keeps a fast rank's next-step traffic out of a slow rank's current-step slots.
-constexpr int SLAB_ACC = 2048, SLAB_MAXW = 8, SLAB_SLOT_FLOATS = SLAB_ACC * (1 + SLAB_MAXW) + 64, SLAB_SLOTS = 32;
+constexpr int SLAB_ACC = 2048, SLAB_MAXW = 8, SLAB_SLOT_FLOATS = SLAB_ACC * (1 + SLAB_MAXW) + 64, SLAB_SLOTS = 48;
 struct SlabComm {
     float* const* peers;       // device array [world]: scratch base of every rank (peers[rank] = own)
     int world, rank, slot;
@@ -112,6 +112,14 @@ struct SlabComm {
 };
 __device__ __forceinline__ float* slab_slot(const SlabComm& c, int peer) {
     return c.peers[peer] + ((size_t)(*c.parity) * SLAB_SLOTS + c.slot) * SLAB_SLOT_FLOATS;
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_sys(unsigned* p, unsigned v) {
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 // n floats of the local accumulator are exchanged; returns (in every thread) a pointer to this rank's slot
 __device__ __forceinline__ float* slab_exchange(const SlabComm& c, int n, unsigned nblocks) {
@@ -125,25 +133,31 @@ __device__ __forceinline__ float* slab_exchange(const SlabComm& c, int n, unsign
     }
     __syncthreads();
     if (s_last) {
-        __threadfence();
-        for (int i = threadIdx.x; i < n; i += blockDim.x) {
-            const float v = __ldcg(mine + i);
-            for (int p = 0; p < c.world; ++p) __stcg(slab_slot(c, p) + SLAB_ACC * (1 + c.rank) + i, v);
+        if (c.world == 1) {  // single rank: the local accumulator IS the total
+            if (threadIdx.x == 0) {
+                __threadfence();
+                red_release_sys(cnt + 1, 1u);
+            }
+        } else {
+            __threadfence();
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                const float v = __ldcg(mine + i);
+                for (int p = 0; p < c.world; ++p) __stcg(slab_slot(c, p) + SLAB_ACC * (1 + c.rank) + i, v);
+            }
+            __threadfence_system();
+            __syncthreads();
+            if ((int)threadIdx.x < c.world)
+                red_release_sys(reinterpret_cast<unsigned*>(slab_slot(c, threadIdx.x) + SLAB_ACC * (1 + SLAB_MAXW)) + 1, 1u);
         }
-        __threadfence_system();
-        __syncthreads();
-        if ((int)threadIdx.x < c.world)
-            atomicAdd_system(reinterpret_cast<unsigned*>(slab_slot(c, threadIdx.x) + SLAB_ACC * (1 + SLAB_MAXW)) + 1, 1u);
     }
     if (threadIdx.x == 0) {
-        volatile unsigned* pub = cnt + 1;
-        while (*pub < (unsigned)c.world) __nanosleep(40);
-        __threadfence_system();
+        while (ld_acquire_sys(cnt + 1) < (unsigned)c.world) __nanosleep(20);
     }
     __syncthreads();
     return mine;
 }
 __device__ __forceinline__ float slab_total(const SlabComm& c, const float* mine, int i) {
+    if (c.world == 1) return __ldcv(mine + i);
     float t = 0.f;
     for (int r = 0; r < c.world; ++r) t += __ldcv(mine + SLAB_ACC * (1 + r) + i);
     return t;

@@ -66,6 +66,16 @@ class CapturedTrainStep:
         self._trained_tensors = [t for m in mods for t in list(m.parameters()) + list(m.buffers()) if t.is_floating_point()]
 
     def _body(self):
+        m = self.model
+        if self.with_evaluator and hasattr(m, "_use_engine") and m._use_engine() and "label" in self.static:
+            # fused engine: GAN + evaluator update as ONE schedule (gradient exchanges overlap the other network's compute)
+            m.DexGANGrasp.train()
+            m.DexEvaluator.train()
+            z = self.static_z
+            if z is None:
+                z = torch.randn((self.static["bps_object"].shape[0], m.DexGANGrasp.latentD), dtype=torch.float32, device=m.device)
+            out = m._engine(int(self.static["bps_object"].shape[0])).combined_step(dict(self.static), z, self.is_train_gen)
+            return {k: (v.detach() if torch.is_tensor(v) else v) for k, v in out.items()}
         b = dict(self.static)  # the step mutates the dict (rot_matrix view), never the static tensors
         out = dict(self.model.update_dexgangrasp(b, is_train_gen=self.is_train_gen, Zgen=self.static_z))
         if self.with_evaluator:

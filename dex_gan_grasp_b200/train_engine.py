@@ -238,7 +238,7 @@ class TrainEngine:
         c = a.comm
         c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
         self._pslot += 1
-        assert self._pslot <= 32
+        assert self._pslot <= 48
 
     def _next_slot(self, n=1):
         """index of the next `n` free accumulator slots of this step"""
@@ -539,109 +539,133 @@ class TrainEngine:
             out[k] = v.contiguous()
         return out
 
-    def gan_step(self, real_data, is_train_gen, Zgen):
+    def _gan_d_step(self, d, Zgen):
+        """Generator forward (dexgangrasp.py:772-776) and the discriminator step up to its gradients (:788-793)."""
+        B, dev = self.B, self.dev
+        G, D = self.G, self.D
+        real_tail = [d["rot_matrix"].reshape(B, 9), d["transl"], d["joint_conf"]]
+        self.prep(G)
+        self._tail_pack(G, [Zgen.float().contiguous()], 0, B, 0)
+        self.forward_blocks(G, B, 1, self.xhat)
+        self._gemm(B, self.nJ + 9, [(G.Xlast.data_ptr(), HID, 0, self.Wh.data_ptr(), HID, 0, HID)], bias=self.bh, C32=self.OUT, ldc=32)
+        _native.check(_L().dexgg_gen_pose(self.OUT.data_ptr(), 32, self.nJ, B, self.fake_rot.data_ptr(), self.fake_transl.data_ptr(),
+                                          self.fake_joint.data_ptr(), _st(dev)))
+        self.running_update(G, 1, B)
+        fake_tail = [self.fake_rot, self.fake_transl, self.fake_joint]
+        # real | fake as one double batch with per-half statistics
+        self.prep(D)
+        self._tail_pack(D, real_tail, 0, B, 0)
+        self._tail_pack(D, fake_tail, B, B, 1)
+        self.forward_blocks(D, 2 * B, 2, self.xhat)
+        D.flat_grad.zero_()
+        bw = self.bw
+        self._score_head(D, 2 * B, 2, targets=(1.0, 0.0), dscale=(0.5 * bw / B, 0.5 * bw / B), lscale=(bw / B, bw / B), loss_slot=0)
+        self.running_update(D, 2, B)
+        self.backward_blocks(D, 2 * B, 2, self.xhat, ("rank1", D.dl, D.head.weight, D.head.weight.grad), True, False)
+        self.unfold(D)
+
+    def _gan_g_step(self, d):
+        """D(fake) with the UPDATED discriminator, gradients back into the generator, up to the generator's gradients (:796-815)."""
         m, B, dev = self.model, self.B, self.dev
         G, D = self.G, self.D
-        d = self._dev_batch(real_data, ("bps_object", "rot_matrix", "transl", "joint_conf"))
         real_tail = [d["rot_matrix"].reshape(B, 9), d["transl"], d["joint_conf"]]
+        fake_tail = [self.fake_rot, self.fake_transl, self.fake_joint]
+        bw = self.bw
+        self.prep(D)
+        self._tail_pack(D, fake_tail, 0, B, 0)
+        self.forward_blocks(D, B, 1, self.xhat)
+        self._score_head(D, B, 1, targets=(1.0, 0.0), dscale=(bw / B, 0.0), lscale=(bw / B, 0.0), loss_slot=2, want_db=False)
+        self.running_update(D, 1, B)
+        self.backward_blocks(D, B, 1, self.xhat, ("rank1", D.dl, D.head.weight, None), False, True)
+        src = self._tail_src(fake_tail)
+        st = D.tail_stat[0]
+        targs = (ctypes.byref(src), B, float(B * self.world), st[0].data_ptr(), st[1].data_ptr(), D.gXT[0].data_ptr(), TAILW, 0,
+                 D.gXT[1].data_ptr(), LDXT, HID, self.gPose.data_ptr())
+        if self.world > 1:
+            slot = self._next_slot()
+            _native.check(_L().dexgg_tail_bn_bwd(*targs, 1, self._slot_ptr(slot), _st(dev)))
+            self._allreduce(self._slot_view(slot, 2 * D.n_tail), "bn_bwd")
+            _native.check(_L().dexgg_tail_bn_bwd(*targs, 2, self._slot_ptr(slot), _st(dev)))
+        else:
+            _native.check(_L().dexgg_tail_bn_bwd(*targs, 0, None, _st(dev)))
+        G.flat_grad.zero_()
+        self.dWh.zero_()
+        self.dbh.zero_()
+        rsrc = self._tail_src(real_tail)
+        _native.check(_L().dexgg_gen_loss(self.OUT.data_ptr(), 32, self.nJ, B, float(B), ctypes.byref(rsrc), self.gPose.data_ptr(),
+                                          float(m.transl_coef), float(m.rot_coef), float(m.conf_coef), self.gHeads.data_ptr(), 32,
+                                          self.loss[3:].data_ptr(), self.dbh.data_ptr(), _st(dev)))
+        self._gemm(32, HID, [(self.gHeads.data_ptr(), 32, 1, G.Xlast.data_ptr(), HID, 1, B)], C32=self.dWh, ldc=HID, split_k=max(1, min(32, B // 256)))
+        self._gemm(B, HID, [(self.gHeads.data_ptr(), 32, 0, self.Wh.data_ptr(), HID, 1, 32)], C16=self.gX, ldc=HID)
+        self.backward_blocks(G, B, 1, self.xhat, ("mat", self.gX, HID), True, False)
+        self.unfold(G)
+
+    def _gan_losses(self, is_train_gen):
+        m = self.model
+        if self.world > 1:  # report the global-batch means
+            self._allreduce(self.loss, "grad")
+            self.loss.div_(self.world)
+        vals = self.mix @ self.loss
+        out = {"total_loss_disc": vals[0], "bce_loss_real": vals[1], "bce_loss_fake": vals[2]}
+        if is_train_gen:
+            m.last_loss_dict_gen = {"gen_loss_fake": vals[3], "transl_loss": vals[4], "rot_loss": vals[5], "conf_loss": vals[6],
+                                    "total_loss_gen": vals[7]}
+        out.update(m.last_loss_dict_gen)
+        return out, vals
+
+    def gan_step(self, real_data, is_train_gen, Zgen):
+        m, dev = self.model, self.dev
+        G, D = self.G, self.D
+        d = self._dev_batch(real_data, ("bps_object", "rot_matrix", "transl", "joint_conf"))
         self.loss.zero_()
         self._begin_step()
         G.attach()
         D.attach()
         with torch.cuda.device(dev), torch.no_grad():
             self._input_norm(d["bps_object"])
-            # ---- generator forward (dexgangrasp.py:772-776) ----
-            self.prep(G)
-            self._tail_pack(G, [Zgen.float().contiguous()], 0, B, 0)
-            self.forward_blocks(G, B, 1, self.xhat)
-            self._gemm(B, self.nJ + 9, [(G.Xlast.data_ptr(), HID, 0, self.Wh.data_ptr(), HID, 0, HID)], bias=self.bh, C32=self.OUT, ldc=32)
-            _native.check(_L().dexgg_gen_pose(self.OUT.data_ptr(), 32, self.nJ, B, self.fake_rot.data_ptr(), self.fake_transl.data_ptr(),
-                                              self.fake_joint.data_ptr(), _st(dev)))
-            self.running_update(G, 1, B)
-            fake_tail = [self.fake_rot, self.fake_transl, self.fake_joint]
-            # ---- discriminator step: real | fake as one double batch with per-half statistics (:788-794) ----
-            self.prep(D)
-            self._tail_pack(D, real_tail, 0, B, 0)
-            self._tail_pack(D, fake_tail, B, B, 1)
-            self.forward_blocks(D, 2 * B, 2, self.xhat)
-            D.flat_grad.zero_()
-            bw = self.bw
-            self._score_head(D, 2 * B, 2, targets=(1.0, 0.0), dscale=(0.5 * bw / B, 0.5 * bw / B), lscale=(bw / B, bw / B), loss_slot=0)
-            self.running_update(D, 2, B)
-            self.backward_blocks(D, 2 * B, 2, self.xhat, ("rank1", D.dl, D.head.weight, D.head.weight.grad), True, False)
-            self.unfold(D)
+            self._gan_d_step(d, Zgen)
             m._sync_grads(D.module)
             D.optimizer.step()
             if is_train_gen:
-                # ---- generator step: D(fake) with the updated discriminator, gradients back into the generator (:796-816) ----
-                self.prep(D)
-                self._tail_pack(D, fake_tail, 0, B, 0)
-                self.forward_blocks(D, B, 1, self.xhat)
-                self._score_head(D, B, 1, targets=(1.0, 0.0), dscale=(bw / B, 0.0), lscale=(bw / B, 0.0), loss_slot=2, want_db=False)
-                self.running_update(D, 1, B)
-                self.backward_blocks(D, B, 1, self.xhat, ("rank1", D.dl, D.head.weight, None), False, True)
-                src = self._tail_src(fake_tail)
-                st = D.tail_stat[0]
-                targs = (ctypes.byref(src), B, float(B * self.world), st[0].data_ptr(), st[1].data_ptr(), D.gXT[0].data_ptr(), TAILW, 0,
-                         D.gXT[1].data_ptr(), LDXT, HID, self.gPose.data_ptr())
-                if self.world > 1:
-                    slot = self._next_slot()
-                    _native.check(_L().dexgg_tail_bn_bwd(*targs, 1, self._slot_ptr(slot), _st(dev)))
-                    self._allreduce(self._slot_view(slot, 2 * D.n_tail), "bn_bwd")
-                    _native.check(_L().dexgg_tail_bn_bwd(*targs, 2, self._slot_ptr(slot), _st(dev)))
-                else:
-                    _native.check(_L().dexgg_tail_bn_bwd(*targs, 0, None, _st(dev)))
-                G.flat_grad.zero_()
-                self.dWh.zero_()
-                self.dbh.zero_()
-                rsrc = self._tail_src(real_tail)
-                _native.check(_L().dexgg_gen_loss(self.OUT.data_ptr(), 32, self.nJ, B, float(B), ctypes.byref(rsrc), self.gPose.data_ptr(),
-                                                  float(m.transl_coef), float(m.rot_coef), float(m.conf_coef), self.gHeads.data_ptr(), 32,
-                                                  self.loss[3:].data_ptr(), self.dbh.data_ptr(), _st(dev)))
-                self._gemm(32, HID, [(self.gHeads.data_ptr(), 32, 1, G.Xlast.data_ptr(), HID, 1, B)], C32=self.dWh, ldc=HID, split_k=max(1, min(32, B // 256)))
-                self._gemm(B, HID, [(self.gHeads.data_ptr(), 32, 0, self.Wh.data_ptr(), HID, 1, 32)], C16=self.gX, ldc=HID)
-                self.backward_blocks(G, B, 1, self.xhat, ("mat", self.gX, HID), True, False)
-                self.unfold(G)
+                self._gan_g_step(d)
                 m._sync_grads(G.module)
                 G.optimizer.step()
-            if self.world > 1:  # report the global-batch means
-                self._allreduce(self.loss, "grad")
-                self.loss.div_(self.world)
-            vals = self.mix @ self.loss
-        out = {"total_loss_disc": vals[0], "bce_loss_real": vals[1], "bce_loss_fake": vals[2]}
-        if is_train_gen:
-            gen = {"gen_loss_fake": vals[3], "transl_loss": vals[4], "rot_loss": vals[5], "conf_loss": vals[6], "total_loss_gen": vals[7]}
-            m.last_loss_dict_gen = gen
-        out.update(m.last_loss_dict_gen)
+            out, _ = self._gan_losses(is_train_gen)
         self._bump_versions(self.G, self.D)
         return out
 
-    def evaluator_step(self, data):
-        m, B, dev = self.model, self.B, self.dev
+    def _eva_grads(self, d):
+        """Evaluator forward / backward up to its gradients (dexgangrasp.py:739-752)."""
+        m, B = self.model, self.B
         E = self.E
-        d = self._dev_batch(data, ("bps_object", "rot_matrix", "transl", "label"))
-        m.DexEvaluator.gt_label = d["label"].float().unsqueeze(-1)
         masks = getattr(m.DexEvaluator, "dropout_masks", None)
         p = float(m.DexEvaluator.dout.p)
         drops = [((masks[i] if masks is not None else None), (0.0 if masks is not None else p), i) for i in range(3)]
         if masks is None and p <= 0.0:
             drops = None
+        _native.check(_L().dexgg_bump_counter(self.seed.data_ptr(), _st(self.dev)))
+        self.prep(E)
+        self._tail_pack(E, [d["rot_matrix"].reshape(B, 9), d["transl"]], 0, B, 0)
+        self.forward_blocks(E, B, 1, self.xhat, drops)
+        E.flat_grad.zero_()
+        bw = self.bw
+        lab = m.DexEvaluator.gt_label.reshape(-1).contiguous()
+        self._score_head(E, B, 1, labels=lab, dscale=(bw / B, 0.0), lscale=(bw / B, 0.0), loss_slot=6)
+        self.running_update(E, 1, B)
+        self.backward_blocks(E, B, 1, self.xhat, ("rank1", E.dl, E.head.weight, E.head.weight.grad), True, False, drops)
+        self.unfold(E)
+
+    def evaluator_step(self, data):
+        m, dev = self.model, self.dev
+        E = self.E
+        d = self._dev_batch(data, ("bps_object", "rot_matrix", "transl", "label"))
+        m.DexEvaluator.gt_label = d["label"].float().unsqueeze(-1)
         self.loss[6:7].zero_()
         self._begin_step()
         E.attach()
         with torch.cuda.device(dev), torch.no_grad():
-            _native.check(_L().dexgg_bump_counter(self.seed.data_ptr(), _st(dev)))
             self._input_norm(d["bps_object"])
-            self.prep(E)
-            self._tail_pack(E, [d["rot_matrix"].reshape(B, 9), d["transl"]], 0, B, 0)
-            self.forward_blocks(E, B, 1, self.xhat, drops)
-            E.flat_grad.zero_()
-            bw = self.bw
-            lab = m.DexEvaluator.gt_label.reshape(-1).contiguous()
-            self._score_head(E, B, 1, labels=lab, dscale=(bw / B, 0.0), lscale=(bw / B, 0.0), loss_slot=6)
-            self.running_update(E, 1, B)
-            self.backward_blocks(E, B, 1, self.xhat, ("rank1", E.dl, E.head.weight, E.head.weight.grad), True, False, drops)
-            self.unfold(E)
+            self._eva_grads(d)
             m._sync_grads(E.module)
             E.optimizer.step()
             val = self.loss[6].clone()
@@ -650,6 +674,55 @@ class TrainEngine:
                 val.div_(self.world)
         self._bump_versions(self.E)
         return {"total_loss_eva": val, "bce_loss": val}
+
+    def combined_step(self, data, Zgen, is_train_gen=True):
+        """update_dexgangrasp + update_dexevaluator on the SAME batch (what train.py does per iteration when both networks train,
+        :249-276, and what C5 times) as one schedule: the two updates touch disjoint parameters, so the evaluator's forward /
+        backward runs while the discriminator's gradients cross NVLink, and the evaluator's gradients cross while the generator
+        step computes.  The input BatchNorm statistics / xhat of the shared BPS batch are computed once.  Results are those of
+        the two calls made one after the other."""
+        m, dev = self.model, self.dev
+        G, D, E = self.G, self.D, self.E
+        d = self._dev_batch(data, ("bps_object", "rot_matrix", "transl", "joint_conf", "label"))
+        m.DexEvaluator.gt_label = d["label"].float().unsqueeze(-1)
+        self.loss.zero_()
+        self._begin_step()
+        for n in (G, D, E):
+            n.attach()
+        main = torch.cuda.current_stream(dev)
+        par = self.world > 1
+        if par and getattr(self, "_comm_stream", None) is None:
+            self._comm_stream = torch.cuda.Stream(dev)
+        with torch.cuda.device(dev), torch.no_grad():
+            self._input_norm(d["bps_object"])
+            self._gan_d_step(d, Zgen)
+            if par:
+                side = self._comm_stream
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    m._sync_grads(D.module)
+                    d_done = torch.cuda.Event()
+                    d_done.record(side)
+            self._eva_grads(d)
+            if par:
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    m._sync_grads(E.module)
+                    e_done = torch.cuda.Event()
+                    e_done.record(side)
+                main.wait_event(d_done)
+            D.optimizer.step()
+            if is_train_gen:
+                self._gan_g_step(d)
+                m._sync_grads(G.module)
+                G.optimizer.step()
+            if par:
+                main.wait_event(e_done)
+            E.optimizer.step()
+            out, vals = self._gan_losses(is_train_gen)
+            out["total_loss_eva"] = out["bce_loss"] = vals[8]
+        self._bump_versions(G, D, E)
+        return out
 
     def _bump_versions(self, *nets):
         """Buffers were written through raw pointers: tell torch (the packed eval-mode weights key on the version counters)."""

@@ -199,3 +199,37 @@ def test_eval_forward_after_graph_replays_uses_trained_weights():
     rot, transl, joint, _ = m.DexGANGrasp.generator.native_forward(probe_z, probe_bps, 0.025, False)
     assert float(np.abs(transl.cpu().numpy() - o["transl"]).max()) < tolerances.FP32_TOL * 5
     assert float(np.abs(joint.cpu().numpy() - o["joint_conf"]).max()) < tolerances.FP32_TOL * 5
+
+
+def test_engine_combined_step_equals_sequential_calls():
+    """train_engine.TrainEngine.combined_step (GAN + evaluator update as one schedule, what CapturedTrainStep replays in bf16
+    mode) gives what update_dexgangrasp followed by update_dexevaluator gives: same losses, weights within Adam's noise bound."""
+    from dex_gan_grasp_b200.graph_step import CapturedTrainStep
+    Bs = 256
+    batches = [{k: v.cuda() for k, v in synth.synth_train_batch(Bs, seed=140 + i).items()} for i in range(4)]
+    zs = [synth.synth_latents(Bs, 5, seed=160 + i).cuda() for i in range(4)]
+
+    def fresh():
+        m = _model("bf16")
+        m.DexEvaluator.dout.p = 0.0
+        return m
+    seq = fresh()
+    for i in [0] + list(range(4)):
+        ls = dict(seq.update_dexgangrasp({k: v.clone() for k, v in batches[i].items()}, Zgen=zs[i]))
+        ls.update(seq.update_dexevaluator({k: v.clone() for k, v in batches[i].items()}))
+    cap = fresh()
+    step = CapturedTrainStep(cap, batches[0], warmup=1, example_z=zs[0])
+    for i in range(4):
+        lc = step(batches[i], zs[i])
+    torch.cuda.synchronize()
+    for k in ls:
+        assert abs(float(ls[k]) - float(lc[k])) < 2e-3 * max(1.0, abs(float(ls[k]))), (k, float(ls[k]), float(lc[k]))
+    for name in ("DexGANGrasp", "DexEvaluator"):
+        sa, sb = getattr(seq, name).state_dict(), getattr(cap, name).state_dict()
+        for k in sa:
+            if sa[k].is_floating_point():
+                d = (sa[k].double() - sb[k].double()).abs()
+                assert float(d.max()) <= 2.1e-4 * 5 and float(d.mean()) < 5e-5, (name, k, float(d.max()), float(d.mean()))
+            else:
+                assert int(sa[k]) == int(sb[k]), (name, k)
+    step.close()
