@@ -162,6 +162,37 @@ __device__ __forceinline__ float slab_total(const SlabComm& c, const float* mine
     for (int r = 0; r < c.world; ++r) t += __ldcv(mine + SLAB_ACC * (1 + r) + i);
     return t;
 }
+// Small collective over the same peer scratch (the statistics of the input / tail BatchNorm and the tail backward sums: a few
+// hundred floats that would otherwise each cost an NCCL launch): CTA b owns the 2048-float chunk b of `src` and slot c.slot + b.
+// It stores its chunk into slice[rank] of every rank's slot, flags, waits for all ranks, then writes the rank-ordered sum to
+// sum_out (may alias src) and / or every rank's chunk to gather_out [world, n].
+__global__ void __launch_bounds__(256) p2p_small_kernel(SlabComm c, const float* src, int n, float* sum_out, float* gather_out) {
+    c.slot += blockIdx.x;
+    const int i0 = blockIdx.x * SLAB_ACC, m = (n - i0 < SLAB_ACC) ? n - i0 : SLAB_ACC;
+    float* mine = slab_slot(c, c.rank);
+    unsigned* cnt = reinterpret_cast<unsigned*>(mine + SLAB_ACC * (1 + SLAB_MAXW));
+    for (int i = threadIdx.x; i < m; i += blockDim.x) {
+        const float v = src[i0 + i];
+        for (int p = 0; p < c.world; ++p) __stcg(slab_slot(c, p) + SLAB_ACC * (1 + c.rank) + i, v);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < c.world) red_release_sys(reinterpret_cast<unsigned*>(slab_slot(c, threadIdx.x) + SLAB_ACC * (1 + SLAB_MAXW)) + 1, 1u);
+    if (threadIdx.x == 0) {
+        while (ld_acquire_sys(cnt + 1) < (unsigned)c.world) __nanosleep(20);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < m; i += blockDim.x) {
+        float t = 0.f;
+        for (int r = 0; r < c.world; ++r) {
+            const float v = __ldcv(mine + SLAB_ACC * (1 + r) + i);
+            t += v;
+            if (gather_out) gather_out[(int64_t)r * n + i0 + i] = v;
+        }
+        if (sum_out) sum_out[i0 + i] = t;
+    }
+}
+
 // flips the step parity and zeroes the OTHER parity buffer (used by the next step)
 __global__ void slab_step_begin_kernel(float* base, unsigned* parity) {
     __shared__ unsigned s_p;
@@ -195,7 +226,7 @@ struct BnFwd {
     SlabComm comm;                 // mode 0
 };
 
-__global__ void __launch_bounds__(256) bn_fwd_slab_kernel(const BnFwd a) {
+__global__ void __launch_bounds__(256, 3) bn_fwd_slab_kernel(const BnFwd a) {
     __shared__ float sm[8 * 2 * 2 * 8 + 2 * 2 * 8];
     const int sub = threadIdx.x & 1, rl = threadIdx.x >> 1, g = blockIdx.z;
     const int c0 = blockIdx.x * 16 + sub * 8;
@@ -298,7 +329,7 @@ struct BnBwd {
     SlabComm comm;                              // mode 0
 };
 
-__global__ void __launch_bounds__(256) bn_bwd_slab_kernel(const BnBwd a) {
+__global__ void __launch_bounds__(256, 2) bn_bwd_slab_kernel(const BnBwd a) {
     __shared__ float sm[8 * 2 * 4 * 8 + 2 * 4 * 8];
     const int sub = threadIdx.x & 1, rl = threadIdx.x >> 1, gi = blockIdx.z;
     const int c0 = blockIdx.x * 16 + sub * 8;
@@ -965,10 +996,12 @@ static int slab_comm(const dexgg_slab_comm& q, int mode, const float* acc, int n
     return DEXGG_OK;
 }
 
-// (column slabs, row splits, groups) with at most one CTA per SM in total: the kernels synchronise the grid with a barrier
-static dim3 slab_grid(int C, int64_t rows_per_group, int n_groups) {
+// (column slabs, row splits, groups) with at most `per_sm` CTAs per SM in total (the occupancy __launch_bounds__ guarantees): every
+// CTA of the grid is resident at once, which the in-kernel exchange needs; more CTAs = more loads in flight for these
+// latency-bound streaming passes
+static dim3 slab_grid(int C, int64_t rows_per_group, int n_groups, int per_sm) {
     const int slabs = C / 16;
-    int rs = sm_count() / (slabs * n_groups);
+    int rs = per_sm * sm_count() / (slabs * n_groups);
     const int64_t max_rs = (rows_per_group + 127) / 128;
     if (rs > max_rs) rs = (int)max_rs;
     if (rs < 1) rs = 1;
@@ -989,7 +1022,7 @@ extern "C" int dexgg_bn_fwd_slab(const dexgg_bn_fwd* q, void* stream) {
     a.mask = q->drop_mask; a.ldm = q->ldm; a.drop_p = q->drop_p; a.seed = q->drop_seed; a.stream = q->drop_stream;
     a.y = static_cast<__nv_bfloat16*>(q->y); a.ldy = q->ldy; a.mode = q->mode; a.acc = q->acc;
     if (int rc = slab_comm(q->comm, q->mode, q->acc, q->n_groups * 2 * q->C, a.comm)) return rc;
-    bn_fwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups), 256, 0, TF_ST>>>(a);
+    bn_fwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups, 3), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_fwd_slab_kernel");
     return DEXGG_OK;
@@ -1012,7 +1045,7 @@ extern "C" int dexgg_bn_bwd_slab(const dexgg_bn_bwd* q, void* stream) {
     a.skip = static_cast<const __nv_bfloat16*>(q->skip); a.lds = q->lds; a.gskip = static_cast<__nv_bfloat16*>(q->gskip); a.ldgs = q->ldgs;
     a.dbias_skip = q->dbias_skip; a.mode = q->mode; a.acc = q->acc;
     if (int rc = slab_comm(q->comm, q->mode, q->acc, q->n_groups * 2 * q->C, a.comm)) return rc;
-    bn_bwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups), 256, 0, TF_ST>>>(a);
+    bn_bwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups, 2), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_bwd_slab_kernel");
     return DEXGG_OK;
@@ -1233,6 +1266,20 @@ extern "C" int dexgg_peer_free(void* ptr) {
     if (ptr) DEXGG_CUDA_OK(cudaFree(ptr));
     return DEXGG_OK;
 }
+// sum (in place if sum_out == src) and / or gather n floats across the ranks through the peer scratch; uses ceil(n / 2048) slots
+extern "C" int dexgg_p2p_small(const dexgg_slab_comm* q, const float* src, int n, float* sum_out, float* gather_out, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(q && src && n >= 1 && (sum_out || gather_out), "p2p_small: bad arguments");
+    const int nb = (n + SLAB_ACC - 1) / SLAB_ACC;
+    SlabComm c;
+    if (int rc = slab_comm(*q, 0, nullptr, 1, c)) return rc;
+    DEXGG_REQUIRE(q->slot + nb <= SLAB_SLOTS, "p2p_small: out of exchange slots");
+    p2p_small_kernel<<<nb, 256, 0, TF_ST>>>(c, src, n, sum_out, gather_out);
+    count_launches(1);
+    DEXGG_LAUNCH_OK("p2p_small_kernel");
+    return DEXGG_OK;
+}
+
 // start of a training step: flip the parity word, zero the other parity buffer for the next step
 extern "C" int dexgg_slab_step_begin(void* scratch_base, unsigned* parity, void* stream) {
     DEXGG_ARCH_OK();

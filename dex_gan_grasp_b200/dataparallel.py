@@ -17,7 +17,8 @@ def is_parallel():
 # Every collective of the training step goes through all_reduce_sum, which counts calls and bytes per kind ("grad",
 # "bn_fwd", "bn_bwd"): bench.py reports them per step (the host counters also advance during a CUDA-graph capture, which is
 # how CapturedTrainStep knows what one replay holds).
-_COUNTERS = {"grad_calls": 0, "grad_bytes": 0, "bn_fwd_calls": 0, "bn_fwd_bytes": 0, "bn_bwd_calls": 0, "bn_bwd_bytes": 0}
+# "p2p_calls": exchanges done INSIDE a kernel over NVLink peer memory (train_engine.py), no NCCL launch
+_COUNTERS = {"grad_calls": 0, "grad_bytes": 0, "bn_fwd_calls": 0, "bn_fwd_bytes": 0, "bn_bwd_calls": 0, "bn_bwd_bytes": 0, "p2p_calls": 0}
 
 
 def collective_counters():

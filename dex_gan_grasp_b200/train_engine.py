@@ -24,7 +24,7 @@ import torch.distributed as dist
 from . import _native
 import os
 
-from ._native import BnBwd, BnFwd, FirstLayer, Gemm, PlainJob, RunEntry, ScoreHead, TailSrc, WeightJobs
+from ._native import BnBwd, BnFwd, FirstLayer, Gemm, PlainJob, RunEntry, ScoreHead, SlabComm, TailSrc, WeightJobs
 
 BPS, HID, INNER, NCAT = 4096, 512, 256, 768
 TAILW = 64          # the tail columns are stored 64 wide (zero padded): 128-byte rows for TMA, N tiles of 64 for the dgrad
@@ -236,9 +236,12 @@ class TrainEngine:
 
     def _comm(self, a):
         c = a.comm
+        from . import dataparallel
         c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
         self._pslot += 1
         assert self._pslot <= 48
+        if self.world > 1:
+            dataparallel._COUNTERS["p2p_calls"] = dataparallel._COUNTERS.get("p2p_calls", 0) + 1
 
     def _next_slot(self, n=1):
         """index of the next `n` free accumulator slots of this step"""
@@ -254,15 +257,33 @@ class TrainEngine:
         return self.scratch[self.SLOT * i:self.SLOT * i + numel]
 
     def _allreduce(self, t, kind):
+        """Cross-rank sum of a small fp32 buffer: through the peer scratch (one launch) or NCCL."""
+        if self.p2p and self.world > 1 and t.numel() <= 4 * 2048 and t.is_contiguous() and t.dtype == torch.float32:
+            self._p2p_small(t, sum_out=t)
+            return
         from . import dataparallel
         dataparallel.all_reduce_sum(t, kind)
+
+    def _p2p_small(self, src, sum_out=None, gather_out=None):
+        from . import dataparallel
+        c = SlabComm()
+        n = src.numel()
+        nb = (n + 2047) // 2048
+        c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
+        self._pslot += nb
+        assert self._pslot <= 48
+        dataparallel._COUNTERS["p2p_calls"] = dataparallel._COUNTERS.get("p2p_calls", 0) + 1
+        _native.check(_L().dexgg_p2p_small(ctypes.byref(c), src.data_ptr(), n, _native.ptr(sum_out), _native.ptr(gather_out), _st(self.dev)))
 
     def _gather_merge(self, local, n_sets, C, n_local, mean, invstd, var=None, kind="bn_fwd"):
         """local [n_sets, 2, C] = per-rank (mean, M2) -> all_gather -> Chan merge (equal row counts) -> mean / invstd [/ var] [n_sets, C]"""
         from . import dataparallel
         W = self.world
         gathered = torch.empty((W,) + tuple(local.shape), dtype=torch.float32, device=self.dev)
-        dataparallel.all_gather(gathered, local.contiguous(), kind)
+        if self.p2p and local.numel() <= 4 * 2048:
+            self._p2p_small(local.contiguous(), gather_out=gathered)
+        else:
+            dataparallel.all_gather(gathered, local.contiguous(), kind)
         _native.check(_L().dexgg_bn_merge(gathered.data_ptr(), W, n_sets, C, float(n_local), EPS, mean, invstd, var, _st(self.dev)))
 
     def _begin_step(self):

@@ -227,6 +227,9 @@ int dexgg_peer_open(const unsigned char* handle64, void** ptr);
 int dexgg_peer_close(void* ptr);
 int dexgg_peer_free(void* ptr);
 int dexgg_slab_step_begin(void* scratch_base, unsigned* parity, void* stream);
+/* small cross-rank sum (sum_out, may alias src) and / or gather (gather_out [world, n]) of n floats through the same peer scratch:
+ * one launch, no NCCL; takes ceil(n / 2048) slots starting at comm->slot */
+int dexgg_p2p_small(const dexgg_slab_comm* comm, const float* src, int n, float* sum_out, float* gather_out, void* stream);
 
 /* Train-mode BatchNorm1d forward as ONE kernel: batch statistics of x per group of rows_per_group rows (the discriminator's
  * real and fake batches are two groups of one call), y = [dropout] LeakyReLU(gamma * xhat + beta [+ residual]).  A CTA owns
