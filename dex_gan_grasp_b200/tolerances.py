@@ -22,10 +22,17 @@ BF16_PIPELINE_EPS = 1e-2
 # bf16 tensor-core TRAINING step (C5) against the fp32 oracle step from identical state: losses relative, gradients in the
 # relative L2 norm per tensor / per tensor of < 64 elements (head biases: sums of cancelling per-sample terms) / over all
 # gradients of a network concatenated
+# Why gradients cannot be tighter than ~1e-1 per tensor in bf16: a LeakyReLU pre-activation within ROUNDING of zero takes slope 1 in
+# one implementation and 0.2 in the other; in fp32 a handful of the 4096 x 768 pre-activations of a layer do (the fp32 CUDA mode
+# already differs from the fp32 CPU oracle by up to 1.1e-2 on generator.gen_rot.weight at B = 4096 for this reason), in bf16
+# (rounding 2^-9) ~0.3 % of them do.  Worst measured at B = 4096 (tests/test_train_c5_gpu.py prints them): gen_rot.weight 0.148,
+# gen_rot.bias 0.137 (the rot6d head: its gradient also passes the Gram-Schmidt normalisation), every other tensor <= 0.09.
 BF16_TRAIN_LOSS_TOL = 2e-2
-BF16_TRAIN_GRAD_TOL = 2e-1
-BF16_TRAIN_GRAD_TOL_SMALL = 3.5e-1
-BF16_TRAIN_GRAD_TOL_ALL = 5e-2
+BF16_TRAIN_GRAD_TOL = 1.5e-1          # any weight tensor except the rot6d head
+BF16_TRAIN_GRAD_TOL_ROT_HEAD = 2.5e-1  # generator.gen_rot.{weight,bias}
+BF16_TRAIN_GRAD_TOL_SMALL = 3.5e-1    # tensors of < 64 elements (head biases)
+BF16_TRAIN_GRAD_TOL_ALL = 5e-2        # all gradients of a network concatenated
+FP32_TRAIN_GRAD_TOL_C5 = 2e-2         # fp32 mode at B = 4096 (5e-3 at B = 192), the slope flips above
 
 # MAGD on data/eval_batch.pth (north_star)
 MAGD_TOL = 1e-3

@@ -294,7 +294,7 @@ class TrainEngine:
             _native.check(_L().dexgg_slab_step_begin(self._peer_mine, self.parity.data_ptr(), _st(self.dev)))
 
     # ------------------------------------------------------------------------------------------------ kernel wrappers
-    def _gemm(self, M, N, segs, bias=None, act_from=None, C16=None, C32=None, ldc=None, split_k=0, accumulate=0):
+    def _gemm(self, M, N, segs, bias=None, act_from=None, C16=None, C32=None, ldc=None, split_k=0, accumulate=0, tile_n=0):
         g = Gemm()
         g.M, g.N, g.n_seg = int(M), int(N), len(segs)
         for i, (A, lda, a_mn, Bm, ldb, b_mn, K) in enumerate(segs):
@@ -304,7 +304,7 @@ class TrainEngine:
         g.act_from = int(N if act_from is None else act_from)
         g.C16 = C16.data_ptr() if C16 is not None else None
         g.C32 = C32.data_ptr() if C32 is not None else None
-        g.ldc, g.accumulate, g.split_k, g.tile_n = int(ldc), int(accumulate), int(split_k), 0
+        g.ldc, g.accumulate, g.split_k, g.tile_n = int(ldc), int(accumulate), int(split_k), int(tile_n)
         _native.check(_L().dexgg_gemm_bf16(ctypes.byref(g), _st(self.dev)))
 
     def _bn_fwd(self, x, ldx, C, rpg, groups, bn, stat, y, ldy, res=None, ldr=0, drop=None):
@@ -509,8 +509,9 @@ class TrainEngine:
                          skip=net.T[b][:, INNER:].data_ptr(), lds=NCAT, gskip=net.G13[:, INNER:].data_ptr(), ldgs=NCAT,
                          dbias_skip=net.db13[b][INNER:].data_ptr(), want_wgrad=want_wgrad, drop=(drops[b] if drops else None), **kw)
             if want_wgrad:  # dW2 = GY^T . H  (both operands MN-major, contraction over the rows split over CTAs)
+                # [512 x 256] output, contraction over the rows: 64-column tiles x 8-way split = 128 CTAs, 8 atomic adds per element
                 self._gemm(HID, INNER, [(net.GY.data_ptr(), HID, 1, net.H[b].data_ptr(), INNER, 1, R)], C32=rb.fc2.weight.grad, ldc=INNER,
-                           split_k=max(1, min(32, R // 256)))
+                           split_k=max(1, min(8, R // 512)), tile_n=64)
             self._gemm(R, INNER, [(net.GY.data_ptr(), HID, 0, blk.W2.data_ptr(), INNER, 1, HID)], C16=net.GH, ldc=INNER)
             self._bn_bwd(INNER, rpg, groups, rb.bn1, net.stat1[b], net.T[b].data_ptr(), NCAT, net.H[b].data_ptr(), INNER, net.G13.data_ptr(), NCAT,
                          g=net.GH.data_ptr(), ldg=INNER, want_wgrad=want_wgrad)
