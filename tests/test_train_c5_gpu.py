@@ -97,7 +97,7 @@ def test_c5_gan_step_vs_oracle(oracle_c5, precision):
     w0 = synth.synth_gan_state_dict(SEED)
     for k, v in m.DexGANGrasp.state_dict().items():
         if "running_" in k:
-            tol = 1e-5 if precision == "fp32" else 1e-2
+            tol = 5e-5 if precision == "fp32" else 1e-2  # fp32: 1e-5 per update at B = 192, three updates of the discriminator's buffers here
             assert float((v.cpu() - o["sd"][k]).abs().max()) < tol * max(1.0, float(o["sd"][k].abs().max())), k
         elif v.is_floating_point():
             assert float((v.cpu() - w0[k]).abs().max()) <= 1.05e-4, k  # |Adam step 1| <= lr
