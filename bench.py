@@ -58,6 +58,7 @@ def parse():
     ap.add_argument("--no-train", action="store_true", help="skip the C5 training block of the default line")
     ap.add_argument("--no-strong", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-c1", action="store_true", help="skip the one-object latency block")
     ap.add_argument("--workload", default="c3", choices=["c3", "train"],
                     help="c3 = the headline inference metric (with the C5 block inside); train = C5 as its own line")
     ap.add_argument("--batch", type=int, default=4096, help="global training batch (C5)")
@@ -206,6 +207,84 @@ def gpu_reference_sample(n_objects, n_samples, n_points, dev, repeats=3):
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return n_objects * n_samples, best
+
+
+# --------------------------------------------------------------------------------------------- C1: one object, online latency
+def c1_latency(model, dev, n_iter=200):
+    """Config C1 / the online shape of dexgangrasp_real_robot.py:131-162: ONE real segmented cloud (soft_scrub, 38 663 points,
+    tests/golden/real_clouds_full.npz = the reference's data/real_objects/object/soft_scrub.pcd) -> BPS -> S grasps -> evaluator
+    -> kept grasps, host buffers in and out.  Two ways through the public API:
+      class_surface  BPSEncoder.encode_pcd_with_bps -> DexGanGrasp.generate_grasps(S) -> filter_grasps(thresh) with numpy in /
+                     out exactly like the robot script (four host round trips)
+      pipeline       GraspPipeline.run_host (B = 1, one captured CUDA graph, one H2D of the cloud + z, one D2H of the top-10)
+    p50 / p99 wall-clock per call, against the CPU port of the same sequence."""
+    from dex_gan_grasp_b200 import bps as bps_mod
+    from dex_gan_grasp_b200.pipeline import GraspPipeline
+    path = os.path.join(REPO, "tests", "golden", "real_clouds_full.npz")
+    if not os.path.exists(path):
+        return {"error": "tests/golden/real_clouds_full.npz missing"}
+    cloud = np.load(path)["soft_scrub/cloud"]
+    enc = bps_mod.BPSEncoder({"gpu_ids": [dev.index]})
+    out = {"cloud": "soft_scrub.pcd (reference data/real_objects), %d points" % len(cloud), "iterations": n_iter}
+    pipe = GraspPipeline(model.DexGANGrasp, model.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025, use_graph=True)
+    cloud_h = torch.from_numpy(cloud).unsqueeze(0).pin_memory()
+    for S in (400, 1000):
+        rec = {}
+        # -- class surface, numpy in / out
+        ts = []
+        pts64 = cloud.astype(np.float64)
+        for i in range(n_iter // 4 + 3):
+            t0 = time.perf_counter()
+            b = enc.encode_pcd_with_bps(pts64)
+            g = model.generate_grasps(b, n_samples=S, return_arr=True)
+            try:
+                f = model.filter_grasps(b, g, thresh=THRESH)
+                kept = len(f["transl"])
+            except ValueError:
+                kept = 0
+            ts.append(time.perf_counter() - t0)
+        ts = np.array(ts[3:]) * 1e3
+        rec["class_surface_ms"] = {"p50": float(np.percentile(ts, 50)), "p99": float(np.percentile(ts, 99)), "kept": kept}
+        # -- batched pipeline API with B = 1 (captured graph)
+        z_h = torch.randn((S, 5), generator=torch.Generator().manual_seed(5)).pin_memory()
+        for _ in range(5):
+            pipe.run_host(cloud_h, z_h, S)
+        ts = []
+        for i in range(n_iter):
+            t0 = time.perf_counter()
+            res, h2d, d2h = pipe.run_host(cloud_h, z_h, S)
+            ts.append(time.perf_counter() - t0)
+        ts = np.array(ts) * 1e3
+        rec["pipeline_ms"] = {"p50": float(np.percentile(ts, 50)), "p99": float(np.percentile(ts, 99)), "kept": int(res["count"].sum()),
+                              "h2d_bytes": h2d, "d2h_bytes": d2h}
+        out["S%d" % S] = rec
+    return out
+
+
+def c1_cpu_port(S=400):
+    """The same one-object sequence on the host cores (oracle/: C BPS + torch-CPU networks)."""
+    from dex_gan_grasp_b200 import synth
+    from oracle import nets_oracle as no
+    lib = ctypes.CDLL(os.path.join(REPO, "oracle", "libdexgg_oracle.so"))
+    cloud = np.load(os.path.join(REPO, "tests", "golden", "real_clouds_full.npz"))["soft_scrub/cloud"]
+    basis = np.load(os.path.join(REPO, "dex_gan_grasp_b200", "basis_point_set.npy")).astype(np.float32)
+    sd_gan, sd_eva = synth.synth_gan_state_dict(SEED), synth.synth_eva_state_dict(SEED)
+    vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ts = []
+    for i in range(6):
+        t0 = time.perf_counter()
+        d, idx = np.empty(4096, np.float32), np.empty(4096, np.int32)
+        lib.dexgg_oracle_bps_encode_mt(vp(basis), 4096, vp(cloud), len(cloud), vp(d), vp(idx), min(cores, 256))
+        z = torch.randn((S, 5))
+        g = no.generate_poses(sd_gan, z, torch.from_numpy(np.tile(d, (S, 1))), 0.025)
+        try:
+            no.filter_grasps(sd_eva, d, g, THRESH)
+        except ValueError:
+            pass
+        ts.append(time.perf_counter() - t0)
+    return {"S": S, "ms_p50": float(np.median(ts[1:]) * 1e3), "cores": cores}
 
 
 # --------------------------------------------------------------------------------------------- clocks
@@ -414,7 +493,9 @@ def main():
     model = DexGanGrasp(cfg)
     model.DexGANGrasp.load_state_dict(sd_gan)
     model.DexEvaluator.load_state_dict(sd_eva)
-    pipe = GraspPipeline(model.DexGANGrasp, model.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025)
+    # one captured CUDA graph per step (GraspPipeline use_graph): at 1024 / N clouds per GPU the ~9 launches + allocations that
+    # Python would issue per step cost as much host time as the GPU needs for the step
+    pipe = GraspPipeline(model.DexGANGrasp, model.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025, use_graph=True)
 
     # weak workload: rank r owns global objects [r*B, (r+1)*B); strong: rank r owns shard_objects(B) of the SAME B objects
     ids_weak = list(range(rank * B, (rank + 1) * B))
@@ -458,6 +539,11 @@ def main():
     n0 = L.dexgg_launch_count()
     times, out = time_steps(lambda: pipe.run_device(clouds_d, z_d, S), args.steps, 0)
     launches = (L.dexgg_launch_count() - n0) // max(args.steps, 1)
+    if launches == 0:  # graph replays do not pass through the library's host-side launch counter: count one eager step
+        n1 = L.dexgg_launch_count()
+        pipe._run_eager(clouds_d, z_d, S)
+        torch.cuda.synchronize()
+        launches = L.dexgg_launch_count() - n1
     st_dev = stats(times)
     ms = st_dev["median"]
     kept = int(out["count"].sum().item())
@@ -630,6 +716,16 @@ def main():
                      "sample": f"{Bq} clouds x {S} z", "note": "fp32 CUDA-core MLP mode (within 1e-4 of the reference)"}
         del model32, pipe32
 
+    # ---- C1: one real object, latency through the class surface and through the pipeline API (rank 0) ----
+    c1 = None
+    if rank == 0 and not args.no_c1:
+        try:
+            c1 = c1_latency(model, dev)
+            if not args.no_cpu_baseline:
+                c1["cpu_port"] = c1_cpu_port(400)
+        except Exception as e:
+            c1 = {"error": repr(e)[:300]}
+
     # ---- C5 training block (every rank takes part: NCCL) ----
     del pipe, model, clouds_d, z_d, flush
     torch.cuda.empty_cache()
@@ -665,13 +761,14 @@ def main():
             "config": {"workload": WORKLOAD, "clouds_per_gpu": B, "points": N_POINTS, "samples_per_cloud": S, "topk": TOPK,
                        "thresh": THRESH, "precision": args.precision, "l2": "256 MB flush write between timed iterations",
                        "timing": "per-step CUDA events, median over K steps, max over ranks",
+                       "issue": "one captured CUDA graph per step (GraspPipeline use_graph=True)",
                        "weights": "seeded synthetic state dicts (no trained checkpoints exist offline)"},
             "e2e": {"value": world * M / (ms_e2e_max * 1e-3), "unit": "grasps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e_max, "streams_ms_per_step": [round(r, 4) for r in reps], "mode": "streaming (median of 3 streams of K steps): K steps through GraspPipeline.run_host_pipelined (H2D of step i+1 and D2H of "
                     "step i-1 overlap the compute of step i; every step's inputs come from pinned host memory, every result is read on the host)",
                     "one_step_at_a_time": {"value": world * M / (ms_e2e_sync_max * 1e-3), "ms_per_step": ms_e2e_sync_max}},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "stages": stages, "parity_check": parity,
-            "strong": strong, "train": train, "cpu_baseline": cpu, "gpu_baseline": gpu_base,
+            "strong": strong, "train": train, "c1_latency": c1, "cpu_baseline": cpu, "gpu_baseline": gpu_base,
             "kept_grasps_last_step": kept, "fp32_exact_mode": fp32_line,
         }
         print(json.dumps(line), flush=True)

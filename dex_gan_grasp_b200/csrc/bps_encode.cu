@@ -673,7 +673,9 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
                 const int64_t want = 2ll * 4 * sm_count();  // two waves of 4 CTAs per SM
                 const int64_t have = (int64_t)gx * B;
                 int64_t s = (want + have - 1) / have;
-                const int64_t smax = (max_cloud_points + 2047) / 2048;  // keep >= ~2048 points per split
+                // keep >= ~2048 points per split; a handful of clouds (the online one-object shape, dexgangrasp_real_robot.py:139)
+                // cannot fill the GPU that way: one 1024-point tile per split then
+                const int64_t smax = have < sm_count() ? (max_cloud_points + 1023) / 1024 : (max_cloud_points + 2047) / 2048;
                 if (s > smax) s = smax;
                 if (s < 1) s = 1;
                 if (s > 255) s = 255;

@@ -12,8 +12,11 @@ from . import bps as bps_mod
 
 
 class GraspPipeline:
-    def __init__(self, gan, evaluator, basis=None, k=10, thresh=0.5, z_offset=0.025):
-        """gan: networks.DexGANGrasp, evaluator: networks.DexEvaluator (both on the same CUDA device, eval mode)."""
+    def __init__(self, gan, evaluator, basis=None, k=10, thresh=0.5, z_offset=0.025, use_graph=False):
+        """gan: networks.DexGANGrasp, evaluator: networks.DexEvaluator (both on the same CUDA device, eval mode).
+        use_graph: run_device replays ONE captured CUDA graph per (input buffers, shapes) instead of issuing the ~9 launches
+        from Python - for small per-call work (one object, or 1024 / N objects per GPU) the host would otherwise bound the
+        step.  The returned tensors are then the graph's static outputs: read them before the next call with the same inputs."""
         self.gan, self.eva = gan, evaluator
         self.device = gan.device
         if basis is None:
@@ -23,6 +26,8 @@ class GraspPipeline:
         self._ws = bps_mod._Workspace()
         self._stage = {}
         self._copy_stream = None
+        self.use_graph = bool(use_graph)
+        self._graphs = {}
         gan.eval()
         evaluator.eval()
 
@@ -33,6 +38,37 @@ class GraspPipeline:
         return d
 
     def run_device(self, clouds, z, samples_per_object, z_ready=None):
+        if self.use_graph and z_ready is None:
+            return self._run_graph(clouds, z, samples_per_object)
+        return self._run_eager(clouds, z, samples_per_object, z_ready)
+
+    def _weights_key(self):
+        return tuple((t.data_ptr(), t._version) for net in (self.gan.generator, self.eva) for t in net._native._tensors())
+
+    def _run_graph(self, clouds, z, samples_per_object):
+        """One cudaGraphLaunch per call: the graph is captured the first time this (cloud buffer, latent buffer, shape) is seen
+        and re-captured when the networks' parameters change."""
+        key = (clouds.data_ptr(), tuple(clouds.shape), z.data_ptr(), tuple(z.shape), int(samples_per_object))
+        wkey = self._weights_key()
+        ent = self._graphs.get(key)
+        if ent is None or ent[2] != wkey:
+            dev = self.device
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):  # eager warm-up: packs the weights, grows the workspaces
+                self._run_eager(clouds, z, samples_per_object, None)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = self._run_eager(clouds, z, samples_per_object, None)
+            if len(self._graphs) >= 8:
+                self._graphs.pop(next(iter(self._graphs)))
+            ent = self._graphs[key] = (graph, out, wkey)
+        ent[0].replay()
+        return ent[1]
+
+    def _run_eager(self, clouds, z, samples_per_object, z_ready=None):
         """clouds [B,N,3], z [B*S,latentD] on the device.  Returns a dict of device tensors:
         idx [B,k] i32 (global row ids, -1 padded), count [B], score [B,k], rot_matrix [B,k,3,3], transl [B,k,3],
         joint_conf [B,k,nJ] (views of `packed`; rows beyond count are zero), bps [B,4096], p [M,1]."""
