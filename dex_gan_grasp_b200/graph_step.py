@@ -9,8 +9,9 @@ count in device memory, `dexgg_adam_step_dev`) all replay from one `cudaGraphLau
     step = CapturedTrainStep(model, example_batch)        # 3 eager warm-up steps, then capture
     losses = step(batch)                                   # dict of device tensors (valid until the next call)
 
-Numerics are those of the eager step (same kernels, same order).  Learning-rate changes made by the schedulers after the
-capture are NOT seen by the graph (lr is a kernel argument): re-capture after `update_learning_rate` changes a group.
+Numerics are those of the eager step (same kernels, same order).  The learning rate is a kernel argument frozen into the graph:
+every call compares the optimizers' current group learning rates with the captured ones and RE-CAPTURES the graph when a
+scheduler (`DexGanGrasp.update_learning_rate`, ReduceLROnPlateau once per epoch in train.py) has changed one.
 """
 import torch
 
@@ -46,21 +47,8 @@ class CapturedTrainStep:
                 self._body()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
-        from . import _native
-        L = _native.lib()
-        from . import dataparallel
-        n0 = L.dexgg_launch_count()
-        c0 = dataparallel.collective_counters()
-        self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
-            self.losses = self._body()
-        self.kernels_per_replay = int(L.dexgg_launch_count() - n0)  # dexgg kernel nodes in the graph (host counter during capture)
-        c1 = dataparallel.collective_counters()
-        self.collectives_per_replay = {k: c1[k] - c0[k] for k in c1}  # NCCL collectives (calls / bytes per kind) in the graph
-        for o in self.opts:  # the capture ran the Python side of the step (host counters + 1) without executing a kernel
-            for st in o.state.values():
-                if "step" in st:
-                    st["step"] -= 1
+        self.graph = None
+        self._capture()
         self.eager_steps = warmup
         mods = [model.DexGANGrasp] + ([model.DexEvaluator] if self.with_evaluator else [])
         self._trained_tensors = [t for m in mods for t in list(m.parameters()) + list(m.buffers()) if t.is_floating_point()]
@@ -82,7 +70,33 @@ class CapturedTrainStep:
             out.update(self.model.update_dexevaluator(dict(self.static)))
         return {k: (v.detach() if torch.is_tensor(v) else v) for k, v in out.items()}
 
+    def _lrs(self):
+        return tuple(float(g["lr"]) for o in self.opts for g in o.param_groups)
+
+    def _capture(self):
+        from . import _native, dataparallel
+        L = _native.lib()
+        if getattr(self, "graph", None) is not None:
+            torch.cuda.synchronize(self.model.device)
+            self.graph.reset()
+        n0 = L.dexgg_launch_count()
+        c0 = dataparallel.collective_counters()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.losses = self._body()
+        self.kernels_per_replay = int(L.dexgg_launch_count() - n0)  # dexgg kernel nodes in the graph (host counter during capture)
+        c1 = dataparallel.collective_counters()
+        self.collectives_per_replay = {k: c1[k] - c0[k] for k in c1}  # collectives (calls / bytes per kind) in the graph
+        self.captured_lrs = self._lrs()
+        for o in self.opts:  # the capture ran the Python side of the step (host counters + 1) without executing a kernel
+            for st in o.state.values():
+                if "step" in st:
+                    st["step"] -= 1
+
     def __call__(self, batch, z=None):
+        if self._lrs() != self.captured_lrs:  # a scheduler changed a learning rate: the frozen kernel argument is stale
+            self._capture()
+            self.recaptures = getattr(self, "recaptures", 0) + 1
         for k, v in batch.items():
             if torch.is_tensor(v):
                 self.static[k].copy_(v, non_blocking=True)
