@@ -698,8 +698,9 @@ def main():
 
     fp32_line = None
     if args.precision == "bf16" and not args.no_fp32_line:
-        # secondary: the fp32 CUDA-core mode (1e-4 parity contract) on a quarter of the clouds, same pipeline
-        model32 = DexGanGrasp(dict(cfg, precision="fp32"))
+        # secondary: the 1e-4 parity contract on the TENSOR cores (fp32_tc: bf16 hi + lo pairs, 3 products per MAC, layer by layer)
+        # on a quarter of the clouds, same pipeline; and the CUDA-core fp32 mode beside it
+        model32 = DexGanGrasp(dict(cfg, precision="fp32_tc"))
         model32.DexGANGrasp.load_state_dict(sd_gan)
         model32.DexEvaluator.load_state_dict(sd_eva)
         pipe32 = GraspPipeline(model32.DexGANGrasp, model32.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025)
@@ -712,9 +713,28 @@ def main():
         pipe32.run_device(c32, z32, S)
         b32.record()
         b32.synchronize()
-        fp32_line = {"value": Bq * S / (a32.elapsed_time(b32) * 1e-3), "unit": "grasps/s per GPU", "ms": a32.elapsed_time(b32),
-                     "sample": f"{Bq} clouds x {S} z", "note": "fp32 CUDA-core MLP mode (within 1e-4 of the reference)"}
+        ms32 = a32.elapsed_time(b32)
+        tf32 = 3 * 2.0 * (MAC_PER_GRASP * Bq * S + MAC_PER_OBJECT * Bq) / (ms32 * 1e-3) / 1e12  # 3 bf16 products per MAC are EXECUTED
+        fp32_line = {"value": Bq * S / (ms32 * 1e-3), "unit": "grasps/s per GPU", "ms": ms32, "sample": f"{Bq} clouds x {S} z",
+                     "mode": "fp32_tc: within 1e-4 of the reference on the tensor cores (bf16 hi + lo pairs, hi*hi + lo*hi + hi*lo, fp32 skip branch)",
+                     "roofline": {"bound": "tensor", "executed_tflops": tf32, "peak": pk["bf16_tflops_sustained"],
+                                  "frac": tf32 / pk["bf16_tflops_sustained"], "frac_of_useful_work": tf32 / 3 / pk["bf16_tflops_sustained"],
+                                  "note": "whole pipeline step (BPS and filter included in the time); useful work = executed / 3"}}
         del model32, pipe32
+        mcc = DexGanGrasp(dict(cfg, precision="fp32"))
+        mcc.DexGANGrasp.load_state_dict(sd_gan)
+        mcc.DexEvaluator.load_state_dict(sd_eva)
+        pcc = GraspPipeline(mcc.DexGANGrasp, mcc.DexEvaluator, k=TOPK, thresh=THRESH, z_offset=0.025)
+        Bc = max(B // 16, 1)
+        cc, zc = clouds_d[:Bc].contiguous(), z_d[:Bc * S].contiguous()
+        pcc.run_device(cc, zc, S)
+        torch.cuda.synchronize()
+        a32.record()
+        pcc.run_device(cc, zc, S)
+        b32.record()
+        b32.synchronize()
+        fp32_line["cuda_core_fp32_mode"] = {"value": Bc * S / (a32.elapsed_time(b32) * 1e-3), "unit": "grasps/s per GPU", "sample": f"{Bc} clouds x {S} z"}
+        del mcc, pcc
 
     # ---- C1: one real object, latency through the class surface and through the pipeline API (rank 0) ----
     c1 = None

@@ -53,6 +53,13 @@ struct LinearB16 {  // bf16 operands (K-major, row pitch a multiple of 16 bytes)
     void* C16 = nullptr;   // bf16 output [M, ldc] and / or
     float* C32 = nullptr;  // fp32 output [M, ldc]
     int64_t ldc = 0;
+    // split-bf16 ("fp32 on tensor cores") plumbing: a value v is carried as hi = bf16(v), lo = bf16(v - hi)
+    int split_seg = 0;               // > 0: C16 gets hi at column n, lo at n + split_seg, hi again at n + 2 * split_seg (the [hi|lo|hi]
+                                     // operand layout that pairs with [w_hi|w_hi|w_lo] weights: hi*hi + lo*hi + hi*lo in one GEMM)
+    int c32_from = 1 << 30;          // columns >= c32_from go to C32 ONLY, at column n - c32_from, row pitch ldc32
+    int64_t ldc32 = 0;               // row pitch of C32 when split / c32_from are used (0: ldc)
+    const float* residual32 = nullptr;  // fp32 residual [M, ldr32]
+    int64_t ldr32 = 0;
 };
 int linear_bf16(const LinearB16& p, cudaStream_t st);  // linear_umma.cu
 

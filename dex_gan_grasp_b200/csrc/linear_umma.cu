@@ -32,6 +32,10 @@ struct UmmaParams {
     __nv_bfloat16* C16;              // bf16 output or null
     float* C32;                      // fp32 output or null
     int64_t ldc;
+    int split_seg, c32_from;         // see LinearB16
+    int64_t ldc32;
+    const float* residual32;
+    int64_t ldr32;
 };
 
 __global__ void __launch_bounds__(UM_THREADS, 1)
@@ -117,7 +121,8 @@ linear_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const bool vec_ok = (p.ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.C16) & 15) == 0) &&
                             ((reinterpret_cast<uintptr_t>(p.C32) & 15) == 0) && (p.ldr % 8 == 0) &&
                             ((reinterpret_cast<uintptr_t>(p.residual) & 15) == 0) && (p.ep.ldbase % 4 == 0) &&
-                            ((reinterpret_cast<uintptr_t>(p.ep.base) & 15) == 0);
+                            ((reinterpret_cast<uintptr_t>(p.ep.base) & 15) == 0) && (p.ldc32 % 4 == 0) && (p.ldr32 % 4 == 0) &&
+                            ((reinterpret_cast<uintptr_t>(p.residual32) & 15) == 0) && (p.split_seg % 8 == 0) && (p.c32_from % 32 == 0);
         int it = 0;
         for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
             const int acc = it & 1, aphase = (it >> 1) & 1;
@@ -165,9 +170,48 @@ linear_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                                 }
                             }
                         }
+                        if (p.residual32) {
+                            const float4* rp = reinterpret_cast<const float4*>(p.residual32 + (int64_t)m * p.ldr32 + n);
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) {
+                                const float4 u = rp[q];
+                                v[4 * q] += u.x; v[4 * q + 1] += u.y; v[4 * q + 2] += u.z; v[4 * q + 3] += u.w;
+                            }
+                        }
                         if (p.ep.act) {
 #pragma unroll
                             for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : DEXGG_LRELU_SLOPE * v[j];
+                        }
+                        if (n >= p.c32_from) {  // this column range leaves in fp32 only (the ResBlock skip branch of the split mode)
+                            float4* dst = reinterpret_cast<float4*>(p.C32 + (int64_t)m * p.ldc32 + (n - p.c32_from));
+#pragma unroll
+                            for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                            continue;
+                        }
+                        if (p.split_seg) {  // [hi | lo | hi] operand of the next split GEMM (+ optional fp32 copy)
+                            uint32_t hi[16], lo[16];
+#pragma unroll
+                            for (int h = 0; h < 16; ++h) {
+                                const __nv_bfloat162 b2 = __floats2bfloat162_rn(v[2 * h], v[2 * h + 1]);
+                                hi[h] = *reinterpret_cast<const uint32_t*>(&b2);
+                                const __nv_bfloat162 l2 = __floats2bfloat162_rn(v[2 * h] - __uint_as_float(hi[h] << 16),
+                                                                                v[2 * h + 1] - __uint_as_float(hi[h] & 0xffff0000u));
+                                lo[h] = *reinterpret_cast<const uint32_t*>(&l2);
+                            }
+                            __nv_bfloat16* row = p.C16 + (int64_t)m * p.ldc + n;
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const uint4 uh = make_uint4(hi[4 * q], hi[4 * q + 1], hi[4 * q + 2], hi[4 * q + 3]);
+                                reinterpret_cast<uint4*>(row)[q] = uh;
+                                reinterpret_cast<uint4*>(row + p.split_seg)[q] = make_uint4(lo[4 * q], lo[4 * q + 1], lo[4 * q + 2], lo[4 * q + 3]);
+                                reinterpret_cast<uint4*>(row + 2 * p.split_seg)[q] = uh;
+                            }
+                            if (p.C32 && p.c32_from >= (1 << 30)) {
+                                float4* dst = reinterpret_cast<float4*>(p.C32 + (int64_t)m * p.ldc32 + n);
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+                            }
+                            continue;
                         }
                         if (p.C16) {
                             uint4* dst = reinterpret_cast<uint4*>(p.C16 + (int64_t)m * p.ldc + n);
@@ -183,7 +227,7 @@ linear_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                             }
                         }
                         if (p.C32) {
-                            float4* dst = reinterpret_cast<float4*>(p.C32 + (int64_t)m * p.ldc + n);
+                            float4* dst = reinterpret_cast<float4*>(p.C32 + (int64_t)m * p.ldc32 + n);
 #pragma unroll
                             for (int q = 0; q < 8; ++q) dst[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
                         }
@@ -196,9 +240,21 @@ linear_umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
                                 if (p.ep.bias) x += p.ep.bias[n + j];
                                 if (p.ep.scale) x = fmaf(x, p.ep.scale[n + j], p.ep.shift[n + j]);
                                 if (p.residual) x += __bfloat162float(p.residual[(int64_t)m * p.ldr + n + j]);
+                                if (p.residual32) x += p.residual32[(int64_t)m * p.ldr32 + n + j];
                                 if (p.ep.act) x = x > 0.f ? x : DEXGG_LRELU_SLOPE * x;
-                                if (p.C16) p.C16[(int64_t)m * p.ldc + n + j] = __float2bfloat16_rn(x);
-                                if (p.C32) p.C32[(int64_t)m * p.ldc + n + j] = x;
+                                if (n + j >= p.c32_from) {
+                                    p.C32[(int64_t)m * p.ldc32 + (n + j - p.c32_from)] = x;
+                                } else if (p.split_seg) {
+                                    const __nv_bfloat16 h = __float2bfloat16_rn(x);
+                                    __nv_bfloat16* row = p.C16 + (int64_t)m * p.ldc + n + j;
+                                    row[0] = h;
+                                    row[p.split_seg] = __float2bfloat16_rn(x - __bfloat162float(h));
+                                    row[2 * p.split_seg] = h;
+                                    if (p.C32 && p.c32_from >= (1 << 30)) p.C32[(int64_t)m * p.ldc32 + n + j] = x;
+                                } else {
+                                    if (p.C16) p.C16[(int64_t)m * p.ldc + n + j] = __float2bfloat16_rn(x);
+                                    if (p.C32) p.C32[(int64_t)m * p.ldc32 + n + j] = x;
+                                }
                             }
                         }
                     }
@@ -280,6 +336,9 @@ int linear_bf16(const LinearB16& q, cudaStream_t st) {
     p.M = q.M; p.N = q.N; p.K = q.K; p.BN = BN; p.ep = q.ep; p.ep.residual = nullptr;
     p.residual = reinterpret_cast<const __nv_bfloat16*>(q.residual16); p.ldr = q.ldr;
     p.C16 = reinterpret_cast<__nv_bfloat16*>(q.C16); p.C32 = q.C32; p.ldc = q.ldc;
+    p.split_seg = q.split_seg; p.c32_from = q.c32_from; p.ldc32 = q.ldc32 ? q.ldc32 : q.ldc; p.residual32 = q.residual32; p.ldr32 = q.ldr32;
+    DEXGG_REQUIRE(q.c32_from >= (1 << 30) || q.C32, "linear_bf16: c32_from needs an fp32 output");
+    DEXGG_REQUIRE(!q.split_seg || q.C16, "linear_bf16: split output needs a bf16 output");
     const int ntiles = ((q.M + UM_BM - 1) / UM_BM) * ((q.N + BN - 1) / BN);
     const int grid = ntiles < sm_count() ? ntiles : sm_count();
     linear_umma_kernel<<<grid, UM_THREADS, UM_SMEM_BYTES, st>>>(tmA, tmW, p); ::dexgg::count_launches(1);

@@ -260,6 +260,8 @@ struct dexgg_net {
 };
 
 namespace {
+inline bool is_tc(const dexgg_net* n) { return n->precision != DEXGG_PRECISION_FP32; }        // bf16 tensor-core GEMMs
+inline bool is_split(const dexgg_net* n) { return n->precision == DEXGG_PRECISION_FP32_TC; }  // hi + lo pairs everywhere
 struct Layout {  // column ranges of one ResBlock's input
     int bps_off, tail_off, x_off;  // x_off < 0: no previous-X segment
 };
@@ -311,8 +313,10 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
         DEXGG_CUDA_OK(cudaMemcpyAsync(B.W2, q[6], (size_t)HID * INNER * 4, cudaMemcpyDeviceToDevice, st));
         bn_affine_kernel<<<nblk(HID), 256, 0, st>>>(q[8], q[9], q[10], q[11], HID, n->tmp_a, n->tmp_c); ::dexgg::count_launches(1);
         affine_bias_kernel<<<nblk(HID), 256, 0, st>>>(n->tmp_a, n->tmp_c, q[7], HID, B.sc2, B.sh2); ::dexgg::count_launches(1);
-        if (n->precision == DEXGG_PRECISION_BF16) {
-            const int tw = n->tailw, xo = B.has_x ? HID : 0;
+        if (is_tc(n)) {
+            // bf16: [X (512) | t_hi | t_hi | t_lo];  split: [X_hi | X_hi | X_lo | t_hi | t_hi | t_lo] (pairs with [a_hi | a_lo | a_hi])
+            const bool sp = is_split(n);
+            const int tw = n->tailw, xw = B.has_x ? HID : 0, xo = sp ? 3 * xw : xw;
             DEXGG_CUDA_OK(cudaMemsetAsync(B.Wt16, 0, (size_t)NCAT * B.KT16 * 2, st));
             for (int part = 0; part < 2; ++part) {
                 const float* w = part == 0 ? q[0] : q[12];
@@ -322,10 +326,14 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
                 pack_split_cols_kernel<<<nblk((int64_t)rows * IN_BPS), 256, 0, st>>>(wb, 3 * IN_BPS, 0, IN_BPS, 2 * IN_BPS, w, fin, L.bps_off, IN_BPS, rows); ::dexgg::count_launches(1);
                 DEXGG_CUDA_OK(cudaMemcpyAsync(n->bb_raw + b * NCAT + r0, bias, rows * 4, cudaMemcpyDeviceToDevice, st));
                 __nv_bfloat16* wt = B.Wt16 + (size_t)r0 * B.KT16;
-                if (B.has_x) { pack_cols_bf16_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT16, 0, w, fin, L.x_off, HID, rows); ::dexgg::count_launches(1); }
+                if (B.has_x) {
+                    if (sp) { pack_split_cols_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT16, 0, HID, 2 * HID, w, fin, L.x_off, HID, rows); ::dexgg::count_launches(1); }
+                    else { pack_cols_bf16_kernel<<<nblk((int64_t)rows * HID), 256, 0, st>>>(wt, B.KT16, 0, w, fin, L.x_off, HID, rows); ::dexgg::count_launches(1); }
+                }
                 pack_split_cols_kernel<<<nblk((int64_t)rows * n->n_tail), 256, 0, st>>>(wt, B.KT16, xo, xo + tw, xo + 2 * tw, w, fin, L.tail_off, n->n_tail, rows); ::dexgg::count_launches(1);
             }
-            pack_cols_bf16_kernel<<<nblk((int64_t)HID * INNER), 256, 0, st>>>(B.W2_16, INNER, 0, q[6], INNER, 0, INNER, HID); ::dexgg::count_launches(1);
+            if (sp) { pack_split_cols_kernel<<<nblk((int64_t)HID * INNER), 256, 0, st>>>(B.W2_16, 3 * INNER, 0, INNER, 2 * INNER, q[6], INNER, 0, INNER, HID); ::dexgg::count_launches(1); }
+            else { pack_cols_bf16_kernel<<<nblk((int64_t)HID * INNER), 256, 0, st>>>(B.W2_16, INNER, 0, q[6], INNER, 0, INNER, HID); ::dexgg::count_launches(1); }
         }
     }
     const float* const* h = P + 4 + 14 * n->n_blocks;
@@ -341,9 +349,11 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
         DEXGG_CUDA_OK(cudaMemcpyAsync(n->Wh, h[0], HID * 4, cudaMemcpyDeviceToDevice, st));
         DEXGG_CUDA_OK(cudaMemcpyAsync(n->bh, h[1], 4, cudaMemcpyDeviceToDevice, st));
     }
-    if (gen && n->precision == DEXGG_PRECISION_BF16) {
-        DEXGG_CUDA_OK(cudaMemsetAsync(n->Wh16, 0, (size_t)32 * HID * 2, st));
-        pack_cols_bf16_kernel<<<nblk((int64_t)n->nh * HID), 256, 0, st>>>(n->Wh16, HID, 0, n->Wh, HID, 0, HID, n->nh); ::dexgg::count_launches(1);
+    if (gen && is_tc(n)) {
+        const int hs = is_split(n) ? 3 : 1;
+        DEXGG_CUDA_OK(cudaMemsetAsync(n->Wh16, 0, (size_t)32 * HID * hs * 2, st));
+        if (is_split(n)) { pack_split_cols_kernel<<<nblk((int64_t)n->nh * HID), 256, 0, st>>>(n->Wh16, 3 * HID, 0, HID, 2 * HID, n->Wh, HID, 0, HID, n->nh); ::dexgg::count_launches(1); }
+        else { pack_cols_bf16_kernel<<<nblk((int64_t)n->nh * HID), 256, 0, st>>>(n->Wh16, HID, 0, n->Wh, HID, 0, HID, n->nh); ::dexgg::count_launches(1); }
     }
     DEXGG_LAUNCH_OK("net packing kernels");
     if (n->chain_ok) {
@@ -397,18 +407,18 @@ void carve_net(dexgg_net* n, Carver& c) {
         B.W2 = c.take<float>((size_t)HID * INNER);
         B.sc2 = c.take<float>(HID);
         B.sh2 = c.take<float>(HID);
-        B.KT16 = (B.has_x ? HID : 0) + 3 * n->tailw;
+        B.KT16 = (is_split(n) ? 3 : 1) * (B.has_x ? HID : 0) + 3 * n->tailw;
         B.Wt16 = nullptr;
         B.W2_16 = nullptr;
-        if (n->precision == DEXGG_PRECISION_BF16) {
+        if (is_tc(n)) {
             B.Wt16 = c.take<__nv_bfloat16>((size_t)NCAT * B.KT16);
-            B.W2_16 = c.take<__nv_bfloat16>((size_t)HID * INNER);
+            B.W2_16 = c.take<__nv_bfloat16>((size_t)HID * INNER * (is_split(n) ? 3 : 1));
         }
     }
     n->Wb16 = nullptr; n->Wh16 = nullptr; n->bb_raw = nullptr;
-    if (n->precision == DEXGG_PRECISION_BF16) {
+    if (is_tc(n)) {
         n->Wb16 = c.take<__nv_bfloat16>((size_t)n->nbase * 3 * IN_BPS);
-        n->Wh16 = c.take<__nv_bfloat16>((size_t)32 * HID);
+        n->Wh16 = c.take<__nv_bfloat16>((size_t)32 * HID * (is_split(n) ? 3 : 1));
         n->bb_raw = c.take<float>(n->nbase);
     }
     n->chain_stream = nullptr;
@@ -458,12 +468,13 @@ struct FwdWs {
     float *base, *H;
     char *tail, *T, *XT0, *XT1;
     __nv_bfloat16* Ab16;  // bf16 mode: [n_obj, 3*4096] split of bn(bps)
+    float *R32, *X32;     // split mode: fp32 skip branch [mc, 512], fp32 copy of the last block's output [mc, 512]
     int64_t mc;
-    int es, tw, ldx;
+    int es, tw, ldx, xoff;  // xoff: element offset of the tail columns inside an XT row (512, or 3*512 in split mode)
 };
 size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w) {
     Carver c{static_cast<char*>(ws)};
-    const bool b16 = n->precision == DEXGG_PRECISION_BF16;
+    const bool b16 = is_tc(n), sp = is_split(n);
     // bf16: one chunk = 128 rows per SM, so every layer's tile count is a multiple of the SM count and the chunk's
     // activations (~60 MB) stay resident in the 126 MB L2 between layers
     const int64_t chunk = b16 ? (int64_t)sm_count() * 128 : CHUNK_ROWS;
@@ -471,7 +482,8 @@ size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w
     w.mc = mc;
     w.es = b16 ? 2 : 4;
     w.tw = b16 ? 3 * n->tailw : n->tailw;
-    w.ldx = HID + w.tw;
+    w.xoff = sp ? 3 * HID : HID;
+    w.ldx = w.xoff + w.tw;
     w.base = c.take<float>((size_t)n_obj * n->nbase);
     w.H = c.take<float>((size_t)mc * 32);
     w.tail = c.take<char>((size_t)mc * w.tw * w.es);
@@ -479,6 +491,8 @@ size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w
     w.XT0 = c.take<char>((size_t)mc * w.ldx * w.es);
     w.XT1 = c.take<char>((size_t)mc * w.ldx * w.es);
     w.Ab16 = b16 ? c.take<__nv_bfloat16>((size_t)n_obj * 3 * IN_BPS) : nullptr;
+    w.R32 = sp ? c.take<float>((size_t)mc * HID) : nullptr;
+    w.X32 = sp ? c.take<float>((size_t)mc * HID) : nullptr;
     return c.used;
 }
 
@@ -500,7 +514,7 @@ int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int6
 
 // base[n_obj, nbase] = bn(bps) · W_bpsᵀ + bias    (once per object; for row-wise inputs n_obj == M)
 int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, const FwdWs& w, cudaStream_t st, bool chain = false) {
-    if (n->precision == DEXGG_PRECISION_BF16) {
+    if (is_tc(n)) {
         bps_bn_split_kernel<<<nblk(n_obj * IN_BPS), 256, 0, st>>>(bps, n->in_a, n->in_c, w.Ab16, n_obj); ::dexgg::count_launches(1);
         LinearB16 q;
         q.A = w.Ab16; q.lda = 3 * IN_BPS; q.W = n->Wb16; q.ldw = 3 * IN_BPS;
@@ -522,7 +536,7 @@ void pack_tail(const dexgg_net* n, const FwdWs& w, const float* s0, int n0, cons
     const float* a = affine ? n->tail_a : nullptr;
     const float* c = affine ? n->tail_c : nullptr;
     const int tw = n->tailw;
-    if (n->precision == DEXGG_PRECISION_BF16) {
+    if (is_tc(n)) {
         TailDst16 d{{reinterpret_cast<__nv_bfloat16*>(d0), reinterpret_cast<__nv_bfloat16*>(d1), reinterpret_cast<__nv_bfloat16*>(d2)}, {ld0, ld1, ld2}};
         pack_tail16_kernel<<<nblk(mc * tw), 256, 0, st>>>(s0, n0, s1, n1, s2, n2, a, c, tw, mc, d); ::dexgg::count_launches(1);
     } else {
@@ -540,6 +554,21 @@ int run_block(const dexgg_net* n, int b, const FwdWs& w, const char* A, int64_t 
     e1.scale = B.sc; e1.shift = B.sh; e1.act = 1;
     Epilogue e2;
     e2.scale = B.sc2; e2.shift = B.sh2; e2.act = 1;
+    if (is_split(n)) {
+        // fp32 on the tensor cores: operands are [hi | lo | hi] x [w_hi | w_hi | w_lo].  First layer: the fc1 columns leave as the
+        // split operand of fc2, the fc3 columns (the skip branch) leave in fp32; fc2 adds the fp32 skip and writes the next split
+        // operand (and, for the last block, an fp32 copy for the score head)
+        LinearB16 p;
+        p.A = A; p.lda = lda; p.W = B.Wt16; p.ldw = B.KT16; p.M = (int)mc; p.N = NCAT; p.K = B.KT16; p.ep = e1;
+        p.C16 = w.T; p.ldc = 3 * INNER; p.split_seg = INNER; p.c32_from = INNER; p.C32 = w.R32; p.ldc32 = HID;
+        int rc = linear_bf16(p, st);
+        if (rc) return rc;
+        LinearB16 q;
+        q.A = w.T; q.lda = 3 * INNER; q.W = B.W2_16; q.ldw = 3 * INNER; q.M = (int)mc; q.N = HID; q.K = 3 * INNER; q.ep = e2;
+        q.residual32 = w.R32; q.ldr32 = HID;
+        q.C16 = Xout; q.ldc = w.ldx; q.split_seg = HID; q.C32 = w.X32; q.ldc32 = HID;
+        return linear_bf16(q, st);
+    }
     if (n->precision == DEXGG_PRECISION_BF16) {
         LinearB16 p;
         p.A = A; p.lda = lda; p.W = B.Wt16; p.ldw = B.KT16; p.M = (int)mc; p.N = NCAT; p.K = B.KT16; p.C16 = w.T; p.ldc = NCAT; p.ep = e1;
@@ -569,7 +598,8 @@ extern "C" int dexgg_net_create(int kind, const float* const* params, int n_para
     DEXGG_REQUIRE(out && params, "net_create: null argument");
     DEXGG_REQUIRE(kind >= DEXGG_NET_GENERATOR && kind <= DEXGG_NET_EVALUATOR, "net_create: unknown kind %d", kind);
     DEXGG_REQUIRE(n_params == n_expected(kind), "net_create: kind %d takes %d parameter tensors, got %d", kind, n_expected(kind), n_params);
-    DEXGG_REQUIRE(precision == DEXGG_PRECISION_FP32 || precision == DEXGG_PRECISION_BF16, "net_create: unsupported precision %d", precision);
+    DEXGG_REQUIRE(precision == DEXGG_PRECISION_FP32 || precision == DEXGG_PRECISION_BF16 || precision == DEXGG_PRECISION_FP32_TC,
+                  "net_create: unsupported precision %d", precision);
     DEXGG_REQUIRE(latent_dim >= 1 && latent_dim <= 16 && n_joints >= 1 && n_joints <= 20, "net_create: latent_dim/n_joints out of range");
     for (int i = 0; i < n_params; ++i) DEXGG_REQUIRE(params[i], "net_create: parameter %d is null", i);
     dexgg_net* n = new (std::nothrow) dexgg_net();
@@ -633,7 +663,7 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
     const bool use_chain = net->chain_ok && chain_enabled();
     if ((rc = compute_base(net, bps, n_obj, w, st, use_chain))) return rc;
     const int zD = net->latentD;
-    const bool b16 = net->precision == DEXGG_PRECISION_BF16;
+    const bool b16 = is_tc(net);
     if (use_chain) {
         ChainArgs a;
         chain_common(net, a, w.base, n_obj, rows_per_obj, M);
@@ -642,12 +672,13 @@ extern "C" int dexgg_generator_forward(const dexgg_net* net, const float* bps, i
     }
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
-        pack_tail(net, w, z + r0 * zD, zD, nullptr, 0, nullptr, 0, false, mc, w.tail, w.tw, w.XT0 + HID * w.es, w.ldx, nullptr, 0, st);
+        pack_tail(net, w, z + r0 * zD, zD, nullptr, 0, nullptr, 0, false, mc, w.tail, w.tw, w.XT0 + w.xoff * w.es, w.ldx, nullptr, 0, st);
         if ((rc = run_block(net, 0, w, w.tail, w.tw, (int)rows_per_obj, r0, mc, w.XT0, st))) return rc;
         if ((rc = run_block(net, 1, w, w.XT0, w.ldx, (int)rows_per_obj, r0, mc, w.XT1, st))) return rc;
         if (b16) {
             LinearB16 h;
-            h.A = w.XT1; h.lda = w.ldx; h.W = net->Wh16; h.ldw = HID; h.M = (int)mc; h.N = net->nh; h.K = HID; h.C32 = w.H; h.ldc = 32;
+            const int hk = is_split(net) ? 3 * HID : HID;  // split: heads contract over [X_hi | X_lo | X_hi]
+            h.A = w.XT1; h.lda = w.ldx; h.W = net->Wh16; h.ldw = hk; h.M = (int)mc; h.N = net->nh; h.K = hk; h.C32 = w.H; h.ldc = 32;
             h.ep.bias = net->bh;
             if ((rc = linear_bf16(h, st))) return rc;
         } else {
@@ -679,7 +710,7 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
     if ((rc = compute_base(net, bps, n_obj, w, st, use_chain))) return rc;
     const int nJ = net->nJ;
     const bool disc = kind == DEXGG_NET_DISCRIMINATOR;
-    const bool b16 = net->precision == DEXGG_PRECISION_BF16;
+    const bool b16 = is_tc(net), sp = is_split(net);
     if (use_chain) {
         ChainArgs a;
         chain_common(net, a, w.base, n_obj, rows_per_obj, M);
@@ -689,7 +720,7 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {
         const int64_t mc = (M - r0 < w.mc) ? M - r0 : w.mc;
         pack_tail(net, w, rot + r0 * 9, 9, transl + r0 * 3, 3, disc ? joint + r0 * nJ : nullptr, disc ? nJ : 0, true, mc, w.tail, w.tw,
-                  w.XT0 + HID * w.es, w.ldx, w.XT1 + HID * w.es, w.ldx, st);
+                  w.XT0 + w.xoff * w.es, w.ldx, w.XT1 + w.xoff * w.es, w.ldx, st);
         if ((rc = run_block(net, 0, w, w.tail, w.tw, (int)rows_per_obj, r0, mc, w.XT0, st))) return rc;
         if ((rc = run_block(net, 1, w, w.XT0, w.ldx, (int)rows_per_obj, r0, mc, w.XT1, st))) return rc;
         const char* X = w.XT1;
@@ -697,7 +728,9 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
             if ((rc = run_block(net, 2, w, w.XT1, w.ldx, (int)rows_per_obj, r0, mc, w.XT0, st))) return rc;
             X = w.XT0;
         }
-        if (b16) {
+        if (sp) {  // the last block's fp32 output copy
+            rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(w.X32, HID, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);
+        } else if (b16) {
             rowdot_sigmoid_bf16_kernel<<<nblk(mc, 8), 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(X), w.ldx, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);
         } else {
             rowdot_sigmoid_kernel<<<nblk(mc, 8), 256, 0, st>>>(reinterpret_cast<const float*>(X), w.ldx, net->Wh, net->bh, HID, mc, p + r0); ::dexgg::count_launches(1);

@@ -440,7 +440,8 @@ class DexGanGrasp(object):
         """cfg['precision'] selects the GEMM arithmetic of the training step too: 'fp32' (default, 1e-4 parity with the
         reference) or 'bf16' (tcgen05 tensor cores, fp32 accumulation and fp32 master weights)."""
         from . import train_ops
-        train_ops.set_precision(self.cfg.get("precision", "fp32"))
+        prec = self.cfg.get("precision", "fp32")
+        train_ops.set_precision("fp32" if prec == "fp32_tc" else prec)
 
     def train_engine_name(self):
         return ("hand-scheduled fused step (train_engine.py: gemm_umma.cu + train_fused.cu)" if self._use_engine()

@@ -20,7 +20,10 @@ from . import _native
 from . import utils
 
 KIND_G, KIND_D, KIND_E = 0, 1, 2
-PRECISION = {"fp32": 0, "bf16": 1}
+# cfg["precision"]: "fp32" = CUDA-core GEMMs (1e-4 contract), "bf16" = tcgen05 (headline mode, stated tolerance),
+# "fp32_tc" = the 1e-4 contract ON the tensor cores (bf16 hi + lo pairs, three products per MAC; inference only - training in this
+# mode uses the fp32 path)
+PRECISION = {"fp32": 0, "bf16": 1, "fp32_tc": 2}
 
 
 def get_scheduler(optimizer, cfg):

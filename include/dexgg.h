@@ -100,7 +100,10 @@ typedef struct dexgg_net dexgg_net;
 enum { DEXGG_NET_GENERATOR = 0, DEXGG_NET_DISCRIMINATOR = 1, DEXGG_NET_EVALUATOR = 2 };
 enum {
     DEXGG_PRECISION_FP32 = 0, /* CUDA-core fp32: within 1e-4 abs of the reference's torch fp32 path */
-    DEXGG_PRECISION_BF16 = 1  /* tcgen05 bf16 operands, fp32 accumulation in TMEM */
+    DEXGG_PRECISION_BF16 = 1, /* tcgen05 bf16 operands, fp32 accumulation in TMEM */
+    DEXGG_PRECISION_FP32_TC = 2 /* the 1e-4 contract ON the tensor cores: every activation and weight carried as a bf16 hi + lo
+                                   pair, three products per MAC (hi*hi + lo*hi + hi*lo) in one tcgen05 GEMM of 3x the K,
+                                   fp32 accumulation, fp32 skip branch */
 };
 
 int dexgg_net_create(int kind, const float* const* params, int n_params, int latent_dim, int n_joints, int precision,

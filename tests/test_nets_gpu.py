@@ -363,3 +363,65 @@ def test_pipeline_streaming_equals_one_step_at_a_time(model):
         assert h2d == steps[0][0].numel() * 4 + steps[0][1].numel() * 4 and d2h > 0
         n += 1
     assert n == len(steps)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# fp32_tc: the 1e-4 contract ON the tensor cores (every activation / weight as a bf16 hi + lo pair, hi*hi + lo*hi + hi*lo per
+# MAC in one tcgen05 GEMM, fp32 skip branch).  Same golden vectors and the same TOL as the CUDA-core fp32 mode.
+@pytest.fixture(scope="module")
+def model_tc():
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    m = DexGanGrasp(dict(CFG, precision="fp32_tc"))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(SEED))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(SEED))
+    m.DexGANGrasp.eval()
+    m.DexEvaluator.eval()
+    return m
+
+
+def test_fp32_tc_rowwise_vs_reference_golden(model_tc, eval_batch, nets_golden):
+    m = model_tc
+    bps = torch.from_numpy(eval_batch["bps_object"]).cuda()
+    z = torch.from_numpy(nets_golden["A/z"]).cuda()
+    rot, transl, joint, r6 = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, True)
+    d = {"rot_6D": md(r6, nets_golden["A/rot_6D"]), "rot": md(rot, nets_golden["A/rot_matrix"]), "transl": md(transl, nets_golden["A/transl"]),
+         "joint": md(joint, nets_golden["A/joint_conf"])}
+    p = m.DexEvaluator({"bps_object": bps, "rot_matrix": torch.from_numpy(nets_golden["A/rot_matrix"]),
+                        "transl": torch.from_numpy(nets_golden["A/transl"])})
+    real = {k: torch.from_numpy(eval_batch[k]) for k in ("bps_object", "rot_matrix", "transl", "joint_conf")}
+    d["p_eva"] = md(p, nets_golden["A/p_eva"])
+    d["p_disc_real"] = md(m.DexGANGrasp.discriminator(real), nets_golden["A/p_disc_real"])
+    d["p_eva_real"] = md(m.DexEvaluator(real), nets_golden["A/p_eva_real"])
+    print("fp32_tc vs reference fp32 (row-wise):", d)
+    assert all(v < TOL for v in d.values()), d
+
+
+def test_fp32_tc_shared_bps_and_many_objects(model_tc, nets_golden, bps_golden):
+    m = model_tc
+    z = torch.from_numpy(nets_golden["B/z"]).cuda()
+    bps = torch.from_numpy(nets_golden["B/bps"]).cuda()
+    rot, transl, joint, _ = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
+    assert md(rot, nets_golden["B/rot_matrix"]) < TOL and md(transl, nets_golden["B/transl"]) < TOL and md(joint, nets_golden["B/joint_conf"]) < TOL
+    grasps = {"rot_matrix": nets_golden["B/rot_matrix"].copy(), "transl": nets_golden["B/transl"].copy(),
+              "joint_conf": nets_golden["B/joint_conf"].copy(), "z": nets_golden["B/z"].copy()}
+    p = m.evaluate_grasps(nets_golden["B/bps"], dict(grasps))
+    assert md(p, nets_golden["B/p_eva"]) < TOL
+    # 7 objects x 3000 samples (more than one 148 x 128-row chunk) against the oracle
+    sd_gan, sd_eva = synth.synth_gan_state_dict(SEED), synth.synth_eva_state_dict(SEED)
+    names = list(bps_golden["names"])
+    b7 = np.concatenate([bps_golden[f"{n}/bps"] for n in names])
+    S = 3000
+    zz = synth.synth_latents(7 * S, 5, seed=41)
+    rot, transl, joint, r6 = m.DexGANGrasp.generator.native_forward(zz, torch.from_numpy(b7), 0.025, True)
+    tiled = torch.from_numpy(np.repeat(b7, S, axis=0))
+    o = no.generate_poses(sd_gan, zz, tiled, 0.025)
+    with torch.no_grad():
+        r6o = no.generator_forward(sd_gan, zz, tiled)["rot_6D"]
+        po = no.evaluator_forward(sd_eva, tiled, torch.from_numpy(o["rot_matrix"]), torch.from_numpy(o["transl"]))
+    pe = m.DexEvaluator.native_forward(torch.from_numpy(b7), o["rot_matrix"], o["transl"])
+    pd = m.DexGANGrasp.discriminator.native_forward(torch.from_numpy(b7), o["rot_matrix"], o["transl"], o["joint_conf"])
+    with torch.no_grad():
+        pdo = no.discriminator_forward(sd_gan, tiled, torch.from_numpy(o["rot_matrix"]), torch.from_numpy(o["transl"]), torch.from_numpy(o["joint_conf"]))
+    d = {"r6": md(r6, r6o), "joint": md(joint, o["joint_conf"]), "p_eva": md(pe, po), "p_disc": md(pd, pdo)}
+    print("fp32_tc vs oracle (7 x 3000):", d)
+    assert all(v < TOL for v in d.values()), d

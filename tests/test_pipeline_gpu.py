@@ -75,9 +75,10 @@ def test_bf16_pipeline_topk_set_vs_fp32_oracle():
 
 
 @pytest.mark.gpu
-def test_fp32_pipeline_topk_set_vs_fp32_oracle():
-    out, ref = _run("fp32")
+@pytest.mark.parametrize("precision", ["fp32", "fp32_tc"])
+def test_fp32_pipeline_topk_set_vs_fp32_oracle(precision):
+    out, ref = _run(precision)
     # the pose drift of a 1e-4 generator seen through the evaluator: 4 x FP32_TOL end to end
     rec = pc.check_pipeline(out, ref, S, THRESH, K, 4 * tolerances.FP32_TOL)
-    print("fp32 pipeline vs fp32 oracle pipeline:", rec)
+    print(precision, "pipeline vs fp32 oracle pipeline:", rec)
     assert rec["bps_bit_exact"] and rec["max_dp"] < 4 * tolerances.FP32_TOL and rec["set_mismatches"] == 0, rec
