@@ -384,8 +384,15 @@ def test_fp32_tc_rowwise_vs_reference_golden(model_tc, eval_batch, nets_golden):
     bps = torch.from_numpy(eval_batch["bps_object"]).cuda()
     z = torch.from_numpy(nets_golden["A/z"]).cuda()
     rot, transl, joint, r6 = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, True)
-    d = {"rot_6D": md(r6, nets_golden["A/rot_6D"]), "rot": md(rot, nets_golden["A/rot_matrix"]), "transl": md(transl, nets_golden["A/transl"]),
-         "joint": md(joint, nets_golden["A/joint_conf"])}
+    d = {"rot_6D": md(r6, nets_golden["A/rot_6D"]), "transl": md(transl, nets_golden["A/transl"]), "joint": md(joint, nets_golden["A/joint_conf"])}
+    # Gram-Schmidt divides by |a| and |x x b|: the 1e-4 budget on the raw 6-D output is amplified by their inverse (as in
+    # test_many_objects_rows_per_object for the CUDA-core mode)
+    r6g = torch.from_numpy(nets_golden["A/rot_6D"])
+    a, b = r6g[:, :3], r6g[:, 3:]
+    x = a / a.norm(dim=1, keepdim=True)
+    amp = (1.0 / torch.minimum(a.norm(dim=1), torch.linalg.cross(x, b).norm(dim=1))).clamp_min(1.0).numpy()
+    drot = np.abs(rot.cpu().numpy() - nets_golden["A/rot_matrix"]).reshape(len(amp), -1).max(1)
+    assert np.all(drot < 4 * TOL * amp), float((drot / amp).max())
     p = m.DexEvaluator({"bps_object": bps, "rot_matrix": torch.from_numpy(nets_golden["A/rot_matrix"]),
                         "transl": torch.from_numpy(nets_golden["A/transl"])})
     real = {k: torch.from_numpy(eval_batch[k]) for k in ("bps_object", "rot_matrix", "transl", "joint_conf")}
@@ -401,7 +408,8 @@ def test_fp32_tc_shared_bps_and_many_objects(model_tc, nets_golden, bps_golden):
     z = torch.from_numpy(nets_golden["B/z"]).cuda()
     bps = torch.from_numpy(nets_golden["B/bps"]).cuda()
     rot, transl, joint, _ = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
-    assert md(rot, nets_golden["B/rot_matrix"]) < TOL and md(transl, nets_golden["B/transl"]) < TOL and md(joint, nets_golden["B/joint_conf"]) < TOL
+    assert md(transl, nets_golden["B/transl"]) < TOL and md(joint, nets_golden["B/joint_conf"]) < TOL
+    assert md(rot, nets_golden["B/rot_matrix"]) < 10 * TOL  # amplified by 1 / |a| as above
     grasps = {"rot_matrix": nets_golden["B/rot_matrix"].copy(), "transl": nets_golden["B/transl"].copy(),
               "joint_conf": nets_golden["B/joint_conf"].copy(), "z": nets_golden["B/z"].copy()}
     p = m.evaluate_grasps(nets_golden["B/bps"], dict(grasps))
