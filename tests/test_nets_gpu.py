@@ -409,7 +409,16 @@ def test_fp32_tc_shared_bps_and_many_objects(model_tc, nets_golden, bps_golden):
     bps = torch.from_numpy(nets_golden["B/bps"]).cuda()
     rot, transl, joint, _ = m.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
     assert md(transl, nets_golden["B/transl"]) < TOL and md(joint, nets_golden["B/joint_conf"]) < TOL
-    assert md(rot, nets_golden["B/rot_matrix"]) < 10 * TOL  # amplified by 1 / |a| as above
+    rot_o = torch.from_numpy(nets_golden["B/rot_matrix"])  # golden has no raw rot6d for case B: x = R[:,:,0] is a / |a|, so bound the
+    # error by the same amplification estimated from the oracle's own 6-D output on these inputs
+    sd_gan0 = synth.synth_gan_state_dict(SEED)
+    with torch.no_grad():
+        r6b = no.generator_forward(sd_gan0, torch.from_numpy(nets_golden["B/z"]), torch.from_numpy(np.tile(nets_golden["B/bps"], (256, 1))))["rot_6D"]
+    a, b = r6b[:, :3], r6b[:, 3:]
+    x = a / a.norm(dim=1, keepdim=True)
+    amp = (1.0 / torch.minimum(a.norm(dim=1), torch.linalg.cross(x, b).norm(dim=1))).clamp_min(1.0).numpy()
+    drot = np.abs(rot.cpu().numpy() - rot_o.numpy()).reshape(len(amp), -1).max(1)
+    assert np.all(drot < 4 * TOL * amp), float((drot / amp).max())
     grasps = {"rot_matrix": nets_golden["B/rot_matrix"].copy(), "transl": nets_golden["B/transl"].copy(),
               "joint_conf": nets_golden["B/joint_conf"].copy(), "z": nets_golden["B/z"].copy()}
     p = m.evaluate_grasps(nets_golden["B/bps"], dict(grasps))
