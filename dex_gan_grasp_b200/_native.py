@@ -142,7 +142,7 @@ class ScoreHead(ctypes.Structure):
 
 class FirstLayer(ctypes.Structure):
     _fields_ = [("W1", c_void_p), ("W3", c_void_p), ("b1", c_void_p), ("b3", c_void_p), ("Fin", c_int), ("cmap", c_void_p), ("dmap", c_void_p),
-                ("in_gamma", c_void_p), ("in_beta", c_void_p), ("Wb", c_void_p), ("Wxt", c_void_p), ("ldxt", c_int), ("bias13", c_void_p),
+                ("bps_src0", c_int), ("in_gamma", c_void_p), ("in_beta", c_void_p), ("Wb", c_void_p), ("Wxt", c_void_p), ("ldxt", c_int), ("bias13", c_void_p),
                 ("dWb", c_void_p), ("dWxt", c_void_p), ("db13", c_void_p), ("gW1", c_void_p), ("gW3", c_void_p), ("gb1", c_void_p),
                 ("gb3", c_void_p), ("g_in_gamma", c_void_p), ("g_in_beta", c_void_p)]
 

@@ -670,15 +670,22 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
             const int gx = (P + BPS_THREADS * R - 1) / (BPS_THREADS * R);
             int nsplit = (flags >> 8) & 0xff;
             if (nsplit == 0) {
-                const int64_t want = 2ll * 4 * sm_count();  // two waves of 4 CTAs per SM
-                const int64_t have = (int64_t)gx * B;
-                int64_t s = (want + have - 1) / have;
-                // keep >= ~2048 points per split; a handful of clouds (the online one-object shape, dexgangrasp_real_robot.py:139)
-                // cannot fill the GPU that way: one 1024-point tile per split then
-                const int64_t smax = have < sm_count() ? (max_cloud_points + 1023) / 1024 : (max_cloud_points + 2047) / 2048;
-                if (s > smax) s = smax;
-                if (s < 1) s = 1;
-                if (s > 255) s = 255;
+                // Splits of the point range (merged by atomicMin) so that the grid fills whole waves of 5 resident CTAs per SM:
+                // the smallest split count whose last wave is >= 90 % full, else the fullest; never below one 1024-point tile per
+                // split (a handful of clouds - the online one-object shape, dexgangrasp_real_robot.py:139 - gets one tile per split)
+                const int64_t have = (int64_t)gx * B, slots = 5ll * sm_count();
+                int64_t smax = (max_cloud_points + 1023) / 1024;
+                if (smax > 64) smax = 64;
+                if (smax < 1) smax = 1;
+                int64_t s = 1;
+                double best_eff = 0.0;
+                for (int64_t c = 1; c <= smax; ++c) {
+                    if (have * c >= 16 * slots && c > 1) break;  // many waves already: quantisation is below 6 %
+                    const double waves = (double)(have * c) / (double)slots;
+                    const double eff = waves / (double)((have * c + slots - 1) / slots);
+                    if (eff > best_eff + 1e-9) { best_eff = eff; s = c; }
+                    if (eff >= 0.9) break;
+                }
                 nsplit = (int)s;
             }
             // the filtered kernel addresses chunks with 14 bits: at most 2^14 * 32 points per split

@@ -815,6 +815,7 @@ struct FirstLayer {
     const float *W1, *W3, *b1, *b3;  // fc1.weight [256, Fin], fc3.weight [512, Fin], biases
     int Fin;
     const int *cmap, *dmap;
+    int bps_src0;                    // first input column of the 4096 BPS columns (they are contiguous; BPS column d has BatchNorm index d)
     const float *in_gamma, *in_beta;
     __nv_bfloat16 *Wb, *Wxt; int ldxt;
     float* bias13;                   // [768] = b + W[:, bn cols] . beta
@@ -845,15 +846,26 @@ __global__ void __launch_bounds__(256) prep_weights_kernel(const WeightJobs J) {
         const int n = row % 768;
         const float* w = n < 256 ? L.W1 + (int64_t)n * L.Fin : L.W3 + (int64_t)(n - 256) * L.Fin;
         float acc = 0.f;
-        for (int c = threadIdx.x; c < L.Fin; c += 256) {
-            const int bi = L.cmap[c], d = L.dmap[c];
-            float v = w[c];
+        // the 4096 BPS columns: two adjacent destination columns per thread (bf16x2 stores), gamma / beta read as float2
+        const float* wb = w + L.bps_src0;
+        __nv_bfloat162* drow = reinterpret_cast<__nv_bfloat162*>(L.Wb + (int64_t)n * 4096);
+#pragma unroll 4
+        for (int i = threadIdx.x; i < 2048; i += 256) {
+            const float w0 = wb[2 * i], w1 = wb[2 * i + 1];
+            const float2 g = *reinterpret_cast<const float2*>(L.in_gamma + 2 * i), be = *reinterpret_cast<const float2*>(L.in_beta + 2 * i);
+            acc = fmaf(w0, be.x, fmaf(w1, be.y, acc));
+            drow[i] = __floats2bfloat162_rn(w0 * g.x, w1 * g.y);
+        }
+        // the other columns (previous block's X, per-row tail): through the maps
+        for (int c = threadIdx.x; c < L.Fin - 4096; c += 256) {
+            const int cc = c < L.bps_src0 ? c : c + 4096;
+            const int bi = L.cmap[cc], d = L.dmap[cc];
+            float v = w[cc];
             if (bi >= 0) {
                 acc = fmaf(v, L.in_beta[bi], acc);
                 v *= L.in_gamma[bi];
             }
-            if (d < 4096) L.Wb[(int64_t)n * 4096 + d] = __float2bfloat16_rn(v);
-            else L.Wxt[(int64_t)n * L.ldxt + (d - 4096)] = __float2bfloat16_rn(v);
+            L.Wxt[(int64_t)n * L.ldxt + (d - 4096)] = __float2bfloat16_rn(v);
         }
         red[threadIdx.x] = acc;
         __syncthreads();
@@ -904,6 +916,7 @@ __global__ void __launch_bounds__(256) unfold_grads_kernel(const WeightJobs J) {
     const int bi = L.cmap[c], d = L.dmap[c];
     const float gam = bi >= 0 ? L.in_gamma[bi] : 1.f, bet = bi >= 0 ? L.in_beta[bi] : 0.f;
     float dg = 0.f, dbt = 0.f;
+#pragma unroll 8
     for (int n = n0; n < n0 + 32; ++n) {
         const float gf = d < 4096 ? L.dWb[(int64_t)n * 4096 + d] : L.dWxt[(int64_t)n * L.ldxt + (d - 4096)];
         const float dbn = n < 256 ? 0.f : L.db13[n];
@@ -1155,7 +1168,8 @@ static int weight_jobs(const dexgg_weight_jobs* q, WeightJobs& J) {
     for (int i = 0; i < q->n_first; ++i) {
         const dexgg_first_layer& s = q->first[i];
         FirstLayer& L = J.fl[i];
-        L.W1 = s.W1; L.W3 = s.W3; L.b1 = s.b1; L.b3 = s.b3; L.Fin = s.Fin; L.cmap = s.cmap; L.dmap = s.dmap; L.in_gamma = s.in_gamma;
+        L.W1 = s.W1; L.W3 = s.W3; L.b1 = s.b1; L.b3 = s.b3; L.Fin = s.Fin; L.cmap = s.cmap; L.dmap = s.dmap; L.bps_src0 = s.bps_src0; L.in_gamma = s.in_gamma;
+        DEXGG_REQUIRE(s.bps_src0 >= 0 && s.bps_src0 + 4096 <= s.Fin, "weight jobs: bad bps_src0");
         L.in_beta = s.in_beta; L.Wb = static_cast<__nv_bfloat16*>(s.Wb); L.Wxt = static_cast<__nv_bfloat16*>(s.Wxt); L.ldxt = s.ldxt;
         L.bias13 = s.bias13; L.dWb = s.dWb; L.dWxt = s.dWxt; L.db13 = s.db13; L.gW1 = s.gW1; L.gW3 = s.gW3; L.gb1 = s.gb1; L.gb3 = s.gb3;
         L.g_in_gamma = s.g_in_gamma; L.g_in_beta = s.g_in_beta;

@@ -133,8 +133,17 @@ __global__ void adam_multi_kernel(const AdamChunk* __restrict__ chunks, float lr
 // capture time).  adam_step_inc_kernel bumps it, then every CTA derives the bias corrections from it in double precision.
 __global__ void adam_step_inc_kernel(int* step) { *step += 1; }
 
-__global__ void adam_multi_dev_kernel(const AdamChunk* __restrict__ chunks, float lr, float beta1, float beta2, float eps, float wd,
-                                      const int* __restrict__ step) {
+// one element of torch.optim.Adam (coupled L2 weight decay, bias correction, eps outside the square root)
+__device__ __forceinline__ void adam_one(float& w, float g, float& m, float& v, float lr_bc1, float beta1, float beta2, float eps, float wd,
+                                         float bc2_sqrt) {
+    g = fmaf(wd, w, g);
+    m = beta1 * m + (1.f - beta1) * g;
+    v = beta2 * v + (1.f - beta2) * g * g;
+    w = w - lr_bc1 * (m / (sqrtf(v) / bc2_sqrt + eps));
+}
+
+__global__ void __launch_bounds__(256) adam_multi_dev_kernel(const AdamChunk* __restrict__ chunks, float lr, float beta1, float beta2, float eps,
+                                                             float wd, const int* __restrict__ step) {
     __shared__ float s_bc[2];
     if (threadIdx.x == 0) {
         const int t = *step;
@@ -142,17 +151,28 @@ __global__ void adam_multi_dev_kernel(const AdamChunk* __restrict__ chunks, floa
         s_bc[1] = (float)sqrt(1.0 - pow((double)beta2, (double)t));
     }
     __syncthreads();
-    const float bc1 = s_bc[0], bc2_sqrt = s_bc[1];
+    const float lr_bc1 = lr / s_bc[0], bc2_sqrt = s_bc[1];
     const AdamChunk c = chunks[blockIdx.x];
-    for (int i = threadIdx.x; i < c.n; i += blockDim.x) {
-        const float w = c.w[i];
-        const float g = fmaf(wd, w, c.g[i]);
-        const float m = beta1 * c.m[i] + (1.f - beta1) * g;
-        const float v = beta2 * c.v[i] + (1.f - beta2) * g * g;
+    const bool vec = ((reinterpret_cast<uintptr_t>(c.w) | reinterpret_cast<uintptr_t>(c.g) | reinterpret_cast<uintptr_t>(c.m) |
+                       reinterpret_cast<uintptr_t>(c.v)) & 15) == 0;
+    const int n4 = vec ? c.n / 4 : 0;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) {  // 16-byte accesses: 28 B of HBM traffic per parameter is all this kernel is
+        float4 w = reinterpret_cast<float4*>(c.w)[i], m = reinterpret_cast<float4*>(c.m)[i], v = reinterpret_cast<float4*>(c.v)[i];
+        const float4 g = reinterpret_cast<const float4*>(c.g)[i];
+        adam_one(w.x, g.x, m.x, v.x, lr_bc1, beta1, beta2, eps, wd, bc2_sqrt);
+        adam_one(w.y, g.y, m.y, v.y, lr_bc1, beta1, beta2, eps, wd, bc2_sqrt);
+        adam_one(w.z, g.z, m.z, v.z, lr_bc1, beta1, beta2, eps, wd, bc2_sqrt);
+        adam_one(w.w, g.w, m.w, v.w, lr_bc1, beta1, beta2, eps, wd, bc2_sqrt);
+        reinterpret_cast<float4*>(c.w)[i] = w;
+        reinterpret_cast<float4*>(c.m)[i] = m;
+        reinterpret_cast<float4*>(c.v)[i] = v;
+    }
+    for (int i = 4 * n4 + threadIdx.x; i < c.n; i += blockDim.x) {
+        float w = c.w[i], m = c.m[i], v = c.v[i];
+        adam_one(w, c.g[i], m, v, lr_bc1, beta1, beta2, eps, wd, bc2_sqrt);
+        c.w[i] = w;
         c.m[i] = m;
         c.v[i] = v;
-        const float denom = sqrtf(v) / bc2_sqrt + eps;
-        c.w[i] = w - (lr / bc1) * (m / denom);
     }
 }
 

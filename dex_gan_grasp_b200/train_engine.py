@@ -50,6 +50,8 @@ class _Block:
     def __init__(self, rb, cmap, dmap, has_x, dev):
         self.rb, self.has_x = rb, has_x
         self.Fin = rb.fc1.weight.shape[1]
+        self.bps_src0 = dmap.index(0)  # the 4096 BPS columns are contiguous in every block's input
+        assert dmap[self.bps_src0:self.bps_src0 + BPS] == list(range(BPS)) and cmap[self.bps_src0:self.bps_src0 + BPS] == list(range(BPS))
         self.cmap = torch.tensor(cmap, dtype=torch.int32, device=dev)
         self.dmap = torch.tensor(dmap, dtype=torch.int32, device=dev)
         self.ldxt = LDXT if has_x else TAILW
@@ -98,7 +100,8 @@ class _Net:
         self.p = torch.zeros((R,), **f32)
         # flat gradient buffer; every parameter's .grad is a view into it (one memset to zero, one allreduce to exchange)
         self.params = [p for p in module.parameters()]
-        self.flat_grad = torch.zeros((sum(p.numel() for p in self.params),), **f32)
+        # every slice starts at a multiple of 4 elements (16 bytes): the fused Adam kernel then moves float4s
+        self.flat_grad = torch.zeros((sum((p.numel() + 3) // 4 * 4 for p in self.params),), **f32)
         module._dexgg_flat_grad = self.flat_grad  # dataparallel.allreduce_gradients exchanges this buffer in place
         self.attach()
 
@@ -109,7 +112,7 @@ class _Net:
             n = p.numel()
             if p.grad is None or p.grad.data_ptr() != self.flat_grad.data_ptr() + 4 * off:
                 p.grad = self.flat_grad[off:off + n].view_as(p)
-            off += n
+            off += (n + 3) // 4 * 4
 
 
 def _maps(kind, b, n_tail, Fin):
@@ -413,7 +416,7 @@ class TrainEngine:
         for i, blk in enumerate(net.blocks):
             rb, F = blk.rb, J.first[i]
             F.W1, F.W3, F.b1, F.b3 = rb.fc1.weight.data_ptr(), rb.fc3.weight.data_ptr(), rb.fc1.bias.data_ptr(), rb.fc3.bias.data_ptr()
-            F.Fin, F.cmap, F.dmap = blk.Fin, blk.cmap.data_ptr(), blk.dmap.data_ptr()
+            F.Fin, F.cmap, F.dmap, F.bps_src0 = blk.Fin, blk.cmap.data_ptr(), blk.dmap.data_ptr(), blk.bps_src0
             F.in_gamma, F.in_beta = net.in_bn.weight.data_ptr(), net.in_bn.bias.data_ptr()
             F.Wb, F.Wxt, F.ldxt, F.bias13 = blk.Wb.data_ptr(), blk.Wxt.data_ptr(), blk.ldxt, blk.bias13.data_ptr()
             if grads:

@@ -324,6 +324,7 @@ int dexgg_gen_loss(const float* out, int64_t ldo, int n_joints, int64_t B, float
 typedef struct {
     const float *W1, *W3, *b1, *b3; int Fin;
     const int *cmap, *dmap;
+    int bps_src0;       /* first input column of the 4096 contiguous BPS columns */
     const float *in_gamma, *in_beta;
     void *Wb, *Wxt; int ldxt; float* bias13;
     const float *dWb, *dWxt, *db13;
