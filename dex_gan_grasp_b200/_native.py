@@ -101,7 +101,7 @@ class GemmSeg(ctypes.Structure):
 class Gemm(ctypes.Structure):
     """include/dexgg.h: dexgg_gemm"""
     _fields_ = [("M", c_int), ("N", c_int), ("n_seg", c_int), ("seg", GemmSeg * 3), ("bias", c_void_p), ("act_from", c_int),
-                ("C16", c_void_p), ("C32", c_void_p), ("ldc", c_int64), ("accumulate", c_int), ("split_k", c_int), ("tile_n", c_int)]
+                ("C16", c_void_p), ("C32", c_void_p), ("ldc", c_int64), ("accumulate", c_int), ("split_k", c_int), ("tile_n", c_int), ("split_slice_stride", c_int64)]
 
 
 c_uint, c_ull = ctypes.c_uint, ctypes.c_ulonglong

@@ -37,6 +37,7 @@ struct GemmParams {
     float* C32;
     int64_t ldc;
     int accumulate;            // 1: C32 += (plain read-modify-write, split == 1)
+    int64_t slice_stride;      // split > 1: 0 = atomic accumulation into C32; > 0 = split ks stores its partial sums at C32 + ks * slice_stride
 };
 
 struct GemmMaps {
@@ -177,11 +178,11 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_umma_kernel(const __grid_c
                 tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * 256 + c), r);
                 tmem_ld_wait();
                 const int n = n0 + c;
-                if (m >= p.M || n >= p.N || empty_range) continue;
+                if (m >= p.M || n >= p.N || (empty_range && !p.slice_stride)) continue;
                 float v[32];
 #pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                if (p.split > 1) {  // partial sum of a split contraction: fp32 atomic accumulation (C32 zeroed by the caller)
+                for (int j = 0; j < 32; ++j) v[j] = empty_range ? 0.f : __uint_as_float(r[j]);
+                if (p.split > 1 && !p.slice_stride) {  // partial sum of a split contraction: fp32 atomic accumulation (C32 zeroed by the caller)
                     float* dst = p.C32 + (int64_t)m * p.ldc + n;
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
@@ -212,7 +213,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_umma_kernel(const __grid_c
                         }
                     }
                     if (p.C32) {
-                        float4* dst = reinterpret_cast<float4*>(p.C32 + (int64_t)m * p.ldc + n);
+                        float4* dst = reinterpret_cast<float4*>(p.C32 + (int64_t)ks * p.slice_stride + (int64_t)m * p.ldc + n);
                         if (p.accumulate) {
 #pragma unroll
                             for (int q = 0; q < 8; ++q) {
@@ -230,7 +231,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) gemm_umma_kernel(const __grid_c
                         if (n + j < p.N) {
                             if (p.C16) p.C16[(int64_t)m * p.ldc + n + j] = __float2bfloat16_rn(v[j]);
                             if (p.C32) {
-                                float* d = p.C32 + (int64_t)m * p.ldc + n + j;
+                                float* d = p.C32 + (int64_t)ks * p.slice_stride + (int64_t)m * p.ldc + n + j;
                                 *d = p.accumulate ? *d + v[j] : v[j];
                             }
                         }
@@ -264,7 +265,9 @@ extern "C" int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream) {
     if (g->M == 0) return DEXGG_OK;
     const int split = g->split_k > 1 ? g->split_k : 1;
     DEXGG_REQUIRE(split == 1 || (g->C32 && !g->C16 && !g->bias && g->act_from >= g->N && !g->accumulate),
-                  "gemm_bf16: a split contraction accumulates raw fp32 sums into a zeroed C32 only");
+                  "gemm_bf16: a split contraction produces raw fp32 partial sums only");
+    DEXGG_REQUIRE(g->split_slice_stride >= 0 && g->split_slice_stride % 4 == 0 && (split > 1 || g->split_slice_stride == 0),
+                  "gemm_bf16: bad split_slice_stride");
     int BN = 256;
     if (g->N <= 32) BN = 32;
     else if (g->N <= 64) BN = 64;
@@ -284,6 +287,7 @@ extern "C" int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream) {
     p.M = g->M; p.N = g->N; p.BN = BN; p.n_seg = g->n_seg; p.split = split;
     p.bias = g->bias; p.act_from = g->act_from < 0 ? 0 : g->act_from;
     p.C16 = reinterpret_cast<__nv_bfloat16*>(g->C16); p.C32 = g->C32; p.ldc = g->ldc; p.accumulate = g->accumulate;
+    p.slice_stride = g->split_slice_stride;
     int nkb = 0;
     for (int s = 0; s < GM_MAX_SEG; ++s) { p.kb[s] = 0; p.a_mn[s] = p.b_mn[s] = 0; }
     for (int s = 0; s < g->n_seg; ++s) {

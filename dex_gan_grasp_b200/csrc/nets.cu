@@ -469,9 +469,11 @@ struct FwdWs {
     char *tail, *T, *XT0, *XT1;
     __nv_bfloat16* Ab16;  // bf16 mode: [n_obj, 3*4096] split of bn(bps)
     float *R32, *X32;     // split mode: fp32 skip branch [mc, 512], fp32 copy of the last block's output [mc, 512]
+    float* base_part;     // tensor-core modes: [base_split, n_obj, nbase] partial sums of the split base GEMM
     int64_t mc;
     int es, tw, ldx, xoff;  // xoff: element offset of the tail columns inside an XT row (512, or 3*512 in split mode)
 };
+int base_split(const dexgg_net* n, int64_t n_obj);
 size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w) {
     Carver c{static_cast<char*>(ws)};
     const bool b16 = is_tc(n), sp = is_split(n);
@@ -491,6 +493,7 @@ size_t carve_ws(const dexgg_net* n, int64_t M, int64_t n_obj, void* ws, FwdWs& w
     w.XT0 = c.take<char>((size_t)mc * w.ldx * w.es);
     w.XT1 = c.take<char>((size_t)mc * w.ldx * w.es);
     w.Ab16 = b16 ? c.take<__nv_bfloat16>((size_t)n_obj * 3 * IN_BPS) : nullptr;
+    w.base_part = (b16 && base_split(n, n_obj) > 1) ? c.take<float>((size_t)base_split(n, n_obj) * n_obj * n->nbase) : nullptr;
     w.R32 = sp ? c.take<float>((size_t)mc * HID) : nullptr;
     w.X32 = sp ? c.take<float>((size_t)mc * HID) : nullptr;
     return c.used;
@@ -512,10 +515,47 @@ int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int6
     return DEXGG_OK;
 }
 
+// The hoisted projection is a [n_obj x nbase x 12288] GEMM: 6 - 9 column tiles x n_obj / 128 row tiles, each 192 k-blocks long.
+// Up to a few thousand objects that is far less than one wave of CTAs, so the contraction is split over CTAs (each split stores
+// its partial sums as its own slice, base_finish_kernel adds them with the bias / affine): 86 -> ~35 us at 1024 objects and
+// ~100 -> ~15 us at 128 (the per-GPU share of the strong 8-GPU split).
+int base_split(const dexgg_net* n, int64_t n_obj) {
+    const int64_t tiles = ((n_obj + 127) / 128) * ((n->nbase + 255) / 256);
+    int64_t s = (sm_count() + tiles - 1) / tiles;
+    if (tiles * 2 > sm_count()) s = tiles >= sm_count() ? 1 : 2;
+    if (s > 16) s = 16;
+    return (int)(s < 1 ? 1 : s);
+}
+// out[o, c] = sc[c] * (sum_s part[s, o, c] + bias[c]) + sh[c]
+__global__ void base_finish_kernel(const float* __restrict__ part, int split, int64_t slice, const float* __restrict__ bias,
+                                   const float* __restrict__ sc, const float* __restrict__ sh, int64_t total, int nbase,
+                                   float* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int c = (int)(i % nbase);
+    float v = bias[c];
+    for (int s = 0; s < split; ++s) v += part[s * slice + i];
+    out[i] = sc ? fmaf(v, sc[c], sh[c]) : v;
+}
+
 // base[n_obj, nbase] = bn(bps) · W_bpsᵀ + bias    (once per object; for row-wise inputs n_obj == M)
 int compute_base(const dexgg_net* n, const float* bps, int64_t n_obj, const FwdWs& w, cudaStream_t st, bool chain = false) {
     if (is_tc(n)) {
         bps_bn_split_kernel<<<nblk(n_obj * IN_BPS), 256, 0, st>>>(bps, n->in_a, n->in_c, w.Ab16, n_obj); ::dexgg::count_launches(1);
+        const int split = base_split(n, n_obj);
+        if (split > 1) {
+            dexgg_gemm g = {};
+            g.M = (int)n_obj; g.N = n->nbase; g.n_seg = 1;
+            g.seg[0].A = w.Ab16; g.seg[0].lda = 3 * IN_BPS; g.seg[0].B = n->Wb16; g.seg[0].ldb = 3 * IN_BPS; g.seg[0].K = 3 * IN_BPS;
+            g.act_from = n->nbase; g.C32 = w.base_part; g.ldc = n->nbase; g.split_k = split; g.tile_n = 256;
+            g.split_slice_stride = (int64_t)n_obj * n->nbase;
+            int rc = dexgg_gemm_bf16(&g, st);
+            if (rc) return rc;
+            const int64_t total = (int64_t)n_obj * n->nbase;
+            base_finish_kernel<<<nblk(total), 256, 0, st>>>(w.base_part, split, total, n->bb_raw, chain ? n->chain_sc : nullptr,
+                                                            chain ? n->chain_sh : nullptr, total, n->nbase, w.base); ::dexgg::count_launches(1);
+            return DEXGG_OK;
+        }
         LinearB16 q;
         q.A = w.Ab16; q.lda = 3 * IN_BPS; q.W = n->Wb16; q.ldw = 3 * IN_BPS;
         q.M = (int)n_obj; q.N = n->nbase; q.K = 3 * IN_BPS; q.C32 = w.base; q.ldc = n->nbase;

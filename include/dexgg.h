@@ -203,6 +203,8 @@ typedef struct {
     int accumulate;     /* 1: C32 += result (split_k == 1) */
     int split_k;        /* 0 / 1: no split */
     int tile_n;         /* 0: chosen by the library; else 64 / 128 / 192 / 256 */
+    int64_t split_slice_stride; /* split_k > 1: 0 = atomic accumulation; > 0 = split s writes its partial sums at C32 + s * stride
+                                   (plain stores, deterministic; the caller sums the slices) */
 } dexgg_gemm;
 int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream);
 
