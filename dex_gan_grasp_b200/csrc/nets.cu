@@ -521,8 +521,7 @@ int check_fwd(const dexgg_net* n, int kind, const void* bps, int64_t n_obj, int6
 // ~100 -> ~15 us at 128 (the per-GPU share of the strong 8-GPU split).
 int base_split(const dexgg_net* n, int64_t n_obj) {
     const int64_t tiles = ((n_obj + 127) / 128) * ((n->nbase + 255) / 256);
-    int64_t s = (sm_count() + tiles - 1) / tiles;
-    if (tiles * 2 > sm_count()) s = tiles >= sm_count() ? 1 : 2;
+    int64_t s = sm_count() / tiles;  // the most splits that still fit one wave of CTAs
     if (s > 16) s = 16;
     return (int)(s < 1 ? 1 : s);
 }
