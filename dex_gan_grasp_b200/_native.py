@@ -117,7 +117,7 @@ class BnFwd(ctypes.Structure):
     _fields_ = [("x", c_void_p), ("ldx", c_int64), ("C", c_int), ("rows_per_group", c_int64), ("n_groups", c_int), ("gamma", c_void_p),
                 ("beta", c_void_p), ("shift", c_void_p), ("mean", c_void_p), ("invstd", c_void_p), ("eps", c_float), ("count_total", c_float),
                 ("residual", c_void_p), ("ldr", c_int64), ("act", c_int), ("drop_mask", c_void_p), ("ldm", c_int64), ("drop_p", c_float),
-                ("drop_seed", c_void_p), ("drop_stream", c_uint), ("y", c_void_p), ("ldy", c_int64), ("mode", c_int), ("acc", c_void_p), ("comm", SlabComm)]
+                ("drop_seed", c_void_p), ("drop_stream", c_uint), ("y", c_void_p), ("ldy", c_int64), ("mode", c_int), ("acc", c_void_p), ("comm", SlabComm), ("ctas_per_sm", c_int)]
 
 
 class BnBwd(ctypes.Structure):
@@ -127,7 +127,7 @@ class BnBwd(ctypes.Structure):
                 ("drop_stream", c_uint), ("x", c_void_p), ("ldx", c_int64), ("mean", c_void_p), ("invstd", c_void_p), ("gamma", c_void_p),
                 ("C", c_int), ("rows_per_group", c_int64), ("n_groups", c_int), ("count_total", c_float), ("dgamma", c_void_p),
                 ("dbeta", c_void_p), ("gx", c_void_p), ("ldgx", c_int64), ("skip", c_void_p), ("lds", c_int64), ("gskip", c_void_p),
-                ("ldgs", c_int64), ("dbias_skip", c_void_p), ("mode", c_int), ("acc", c_void_p), ("comm", SlabComm)]
+                ("ldgs", c_int64), ("dbias_skip", c_void_p), ("mode", c_int), ("acc", c_void_p), ("comm", SlabComm), ("ctas_per_sm", c_int)]
 
 
 class TailSrc(ctypes.Structure):

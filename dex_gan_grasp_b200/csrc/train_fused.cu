@@ -1035,7 +1035,7 @@ extern "C" int dexgg_bn_fwd_slab(const dexgg_bn_fwd* q, void* stream) {
     a.mask = q->drop_mask; a.ldm = q->ldm; a.drop_p = q->drop_p; a.seed = q->drop_seed; a.stream = q->drop_stream;
     a.y = static_cast<__nv_bfloat16*>(q->y); a.ldy = q->ldy; a.mode = q->mode; a.acc = q->acc;
     if (int rc = slab_comm(q->comm, q->mode, q->acc, q->n_groups * 2 * q->C, a.comm)) return rc;
-    bn_fwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups, 3), 256, 0, TF_ST>>>(a);
+    bn_fwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups, (q->ctas_per_sm >= 1 && q->ctas_per_sm <= 3) ? q->ctas_per_sm : 3), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_fwd_slab_kernel");
     return DEXGG_OK;
@@ -1058,7 +1058,7 @@ extern "C" int dexgg_bn_bwd_slab(const dexgg_bn_bwd* q, void* stream) {
     a.skip = static_cast<const __nv_bfloat16*>(q->skip); a.lds = q->lds; a.gskip = static_cast<__nv_bfloat16*>(q->gskip); a.ldgs = q->ldgs;
     a.dbias_skip = q->dbias_skip; a.mode = q->mode; a.acc = q->acc;
     if (int rc = slab_comm(q->comm, q->mode, q->acc, q->n_groups * 2 * q->C, a.comm)) return rc;
-    bn_bwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups, 2), 256, 0, TF_ST>>>(a);
+    bn_bwd_slab_kernel<<<slab_grid(q->C, q->rows_per_group, q->n_groups, (q->ctas_per_sm >= 1 && q->ctas_per_sm <= 2) ? q->ctas_per_sm : 2), 256, 0, TF_ST>>>(a);
     count_launches(1);
     DEXGG_LAUNCH_OK("bn_bwd_slab_kernel");
     return DEXGG_OK;

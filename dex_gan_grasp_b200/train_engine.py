@@ -198,6 +198,7 @@ class TrainEngine:
         # per-launch accumulator slots of the column-slab kernels ([2 groups, 2, 512] floats each; the whole scratch is zeroed once
         # at the start of a step and every launch of the step takes the next slot) + the words of their grid barrier
         self.SLOT = 4096
+        self.slab_ctas = 0  # 0: the library's default slab grid; combined_step sets 1 while its two chains run concurrently
         self.world = _world()
         self.rank = dist.get_rank() if self.world > 1 else 0
         self._setup_exchange()
@@ -325,6 +326,7 @@ class TrainEngine:
                 a.drop_mask, a.ldm = mask.data_ptr(), mask.stride(0)
             a.drop_p, a.drop_seed, a.drop_stream = float(p), self.seed.data_ptr(), int(stream)
         a.y, a.ldy, a.mode = y, ldy, 0
+        a.ctas_per_sm = self.slab_ctas
         if self.p2p:
             self._comm(a)
         elif self.world > 1:  # NCCL fallback: local shifted sums -> ONE allreduce -> normalise with the global statistics
@@ -360,6 +362,7 @@ class TrainEngine:
         a.mode = 0
         slot = self._next_slot()
         a.acc = self._slot_ptr(slot)
+        a.ctas_per_sm = self.slab_ctas
         if self.p2p:
             self._comm(a)
         elif self.world > 1:
@@ -702,10 +705,14 @@ class TrainEngine:
 
     def combined_step(self, data, Zgen, is_train_gen=True):
         """update_dexgangrasp + update_dexevaluator on the SAME batch (what train.py does per iteration when both networks train,
-        :249-276, and what C5 times) as one schedule: the two updates touch disjoint parameters, so the evaluator's forward /
-        backward runs while the discriminator's gradients cross NVLink, and the evaluator's gradients cross while the generator
-        step computes.  The input BatchNorm statistics / xhat of the shared BPS batch are computed once.  Results are those of
-        the two calls made one after the other."""
+        :249-276, and what C5 times) as ONE schedule of TWO concurrent chains: the updates touch disjoint parameters, so after the
+        shared input BatchNorm the evaluator's whole update (forward, backward, gradient exchange, Adam) runs on a second stream
+        beside the GAN update.  Neither chain fills the GPU alone - a latency-bound slab / small-GEMM kernel of one chain leaves the
+        tensor cores to a big GEMM of the other, HBM-bound Adam / weight preparation of one runs under the GEMMs of the other, and on
+        N ranks each chain's gradient exchange crosses NVLink under the other's compute.  The slab kernels spin on an in-kernel
+        exchange, so while two chains are in flight their grids are capped at one CTA per SM: any two of them always fit the GPU
+        together (2 x 148 CTAs x 32 K registers), and everything else that may hold an SM (GEMMs, NCCL) ends without waiting on
+        them.  Results are those of the two calls made one after the other."""
         m, dev = self.model, self.dev
         G, D, E = self.G, self.D, self.E
         d = self._dev_batch(data, ("bps_object", "rot_matrix", "transl", "joint_conf", "label"))
@@ -715,35 +722,28 @@ class TrainEngine:
         for n in (G, D, E):
             n.attach()
         main = torch.cuda.current_stream(dev)
-        par = self.world > 1
-        if par and getattr(self, "_comm_stream", None) is None:
-            self._comm_stream = torch.cuda.Stream(dev)
+        if getattr(self, "_side_stream", None) is None:
+            self._side_stream = torch.cuda.Stream(dev)
+        side = self._side_stream
         with torch.cuda.device(dev), torch.no_grad():
             self._input_norm(d["bps_object"])
-            self._gan_d_step(d, Zgen)
-            if par:
-                side = self._comm_stream
+            self.slab_ctas = 1
+            try:
                 side.wait_stream(main)
-                with torch.cuda.stream(side):
-                    m._sync_grads(D.module)
-                    d_done = torch.cuda.Event()
-                    d_done.record(side)
-            self._eva_grads(d)
-            if par:
-                side.wait_stream(main)
-                with torch.cuda.stream(side):
+                with torch.cuda.stream(side):   # chain 2: the evaluator update
+                    self._eva_grads(d)
                     m._sync_grads(E.module)
-                    e_done = torch.cuda.Event()
-                    e_done.record(side)
-                main.wait_event(d_done)
-            D.optimizer.step()
-            if is_train_gen:
-                self._gan_g_step(d)
-                m._sync_grads(G.module)
-                G.optimizer.step()
-            if par:
-                main.wait_event(e_done)
-            E.optimizer.step()
+                    E.optimizer.step()
+                self._gan_d_step(d, Zgen)      # chain 1: the GAN update
+                m._sync_grads(D.module)
+                D.optimizer.step()
+                if is_train_gen:
+                    self._gan_g_step(d)
+                    m._sync_grads(G.module)
+                    G.optimizer.step()
+                main.wait_stream(side)
+            finally:
+                self.slab_ctas = 0
             out, vals = self._gan_losses(is_train_gen)
             out["total_loss_eva"] = out["bce_loss"] = vals[8]
         self._bump_versions(G, D, E)

@@ -256,6 +256,8 @@ typedef struct {
     int mode;
     float* acc;                          /* modes 1 / 2 (NCCL fallback): [n_groups, 2, C] scratch, ZEROED by the caller */
     dexgg_slab_comm comm;                /* mode 0 */
+    int ctas_per_sm;                     /* 0: library default (3 forward / 2 backward); 1 when two step chains run concurrently on
+                                            two streams, so that the grids of two spinning slab kernels always fit the GPU together */
 } dexgg_bn_fwd;
 int dexgg_bn_fwd_slab(const dexgg_bn_fwd* args, void* stream);
 
@@ -276,6 +278,7 @@ typedef struct {
     int mode;                            /* data parallel: 1 = local column sums into acc; 2 = apply with the (allreduced) acc */
     float* acc;                          /* modes 1 / 2: [n_groups, 2, C] scratch, ZEROED by the caller */
     dexgg_slab_comm comm;                /* mode 0 */
+    int ctas_per_sm;
 } dexgg_bn_bwd;
 int dexgg_bn_bwd_slab(const dexgg_bn_bwd* args, void* stream);
 
