@@ -67,6 +67,7 @@ SIGNATURES = {
     "dexgg_peer_free": (c_int, [c_void_p]),
     "dexgg_slab_step_begin": (c_int, [c_void_p, c_void_p, c_void_p]),
     "dexgg_p2p_small": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "dexgg_grad_allreduce": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, ctypes.c_float, c_int, c_void_p]),
     "dexgg_f32_to_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_f32_to_bf16_t": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int, c_void_p]),
     "dexgg_rot6d_forward": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),

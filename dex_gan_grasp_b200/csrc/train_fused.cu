@@ -104,7 +104,7 @@ __device__ __forceinline__ void slab_reduce(float (&acc)[NQ][8], float* sm /* [8
 // The grids hold at most one CTA per SM and run stream-ordered behind their producers, so every CTA is resident while it spins.
 // The parity buffer alternates per step (dexgg_slab_step_begin flips it on the device and zeroes the other one for the next
 // step), which keeps a fast rank's next-step traffic out of a slow rank's current-step slots.
-constexpr int SLAB_ACC = 2048, SLAB_MAXW = 8, SLAB_SLOT_FLOATS = SLAB_ACC * (1 + SLAB_MAXW) + 64, SLAB_SLOTS = 48;
+constexpr int SLAB_ACC = 2048, SLAB_MAXW = 8, SLAB_SLOT_FLOATS = SLAB_ACC * (1 + SLAB_MAXW) + 64, SLAB_SLOTS = 64;
 struct SlabComm {
     float* const* peers;       // device array [world]: scratch base of every rank (peers[rank] = own)
     int world, rank, slot;
@@ -190,6 +190,59 @@ __global__ void __launch_bounds__(256) p2p_small_kernel(SlabComm c, const float*
             if (gather_out) gather_out[(int64_t)r * n + i0 + i] = v;
         }
         if (sum_out) sum_out[i0 + i] = t;
+    }
+}
+
+// Gradient allreduce of a data-parallel step over the SAME peer mapping, one launch, no NCCL: every rank's flat gradient buffer
+// lives in peer-mapped memory (bufs[p] = rank p's buffer as seen from here).  Two-shot: rank r owns the r-th n/world chunk; it
+// reads that chunk from every rank over NVLink, sums in rank order, scales (the 1/world of the mean) and stores the result into
+// the chunk of EVERY rank - so all ranks hold bit-identical gradients.  Two flag barriers through one exchange slot:
+//   ready (cnt[1]): every rank's kernel has started, i.e. its gradients are complete in stream order;
+//   done  (cnt[2]): every owner's stores have landed; only the last CTA of a rank waits for it, which keeps the kernel (and the
+//                   Adam update behind it in the stream) from completing early.
+// A small grid of narrow CTAs (<= 85 registers x 256 threads): it always fits beside the capped slab grid of the other chain of
+// a step, so it may spin while that chain runs - unlike an NCCL kernel, whose CTAs do not fit an SM holding a slab CTA.
+__global__ void __launch_bounds__(256, 3) grad_allreduce_kernel(SlabComm c, float4* const* bufs, long long n4, float scale) {
+    __shared__ int s_last;
+    float* mine = slab_slot(c, c.rank);
+    unsigned* cnt = reinterpret_cast<unsigned*>(mine + SLAB_ACC * (1 + SLAB_MAXW));
+    if (blockIdx.x == 0 && (int)threadIdx.x < c.world)
+        red_release_sys(reinterpret_cast<unsigned*>(slab_slot(c, threadIdx.x) + SLAB_ACC * (1 + SLAB_MAXW)) + 1, 1u);
+    if (threadIdx.x == 0) {
+        while (ld_acquire_sys(cnt + 1) < (unsigned)c.world) __nanosleep(20);
+    }
+    __syncthreads();
+    float4* b[SLAB_MAXW];
+#pragma unroll
+    for (int p = 0; p < SLAB_MAXW; ++p) b[p] = bufs[p < c.world ? p : 0];
+    const long long per = (n4 + c.world - 1) / c.world, lo = per * c.rank, hi = (lo + per < n4) ? lo + per : n4;
+    for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
+        float4 v[SLAB_MAXW];
+#pragma unroll
+        for (int p = 0; p < SLAB_MAXW; ++p)
+            if (p < c.world) v[p] = __ldcg(b[p] + i);
+        float4 t = v[0];
+#pragma unroll
+        for (int p = 1; p < SLAB_MAXW; ++p)
+            if (p < c.world) { t.x += v[p].x; t.y += v[p].y; t.z += v[p].z; t.w += v[p].w; }
+        t.x *= scale; t.y *= scale; t.z *= scale; t.w *= scale;
+#pragma unroll
+        for (int p = 0; p < SLAB_MAXW; ++p)
+            if (p < c.world) __stcg(b[p] + i, t);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_last = atomicAdd(cnt, 1u) == gridDim.x - 1;
+        __threadfence();
+    }
+    __syncthreads();
+    if (s_last) {
+        if ((int)threadIdx.x < c.world)
+            red_release_sys(reinterpret_cast<unsigned*>(slab_slot(c, threadIdx.x) + SLAB_ACC * (1 + SLAB_MAXW)) + 2, 1u);
+        if (threadIdx.x == 0) {
+            while (ld_acquire_sys(cnt + 2) < (unsigned)c.world) __nanosleep(20);
+        }
     }
 }
 
@@ -1291,6 +1344,20 @@ extern "C" int dexgg_p2p_small(const dexgg_slab_comm* q, const float* src, int n
     p2p_small_kernel<<<nb, 256, 0, TF_ST>>>(c, src, n, sum_out, gather_out);
     count_launches(1);
     DEXGG_LAUNCH_OK("p2p_small_kernel");
+    return DEXGG_OK;
+}
+
+// in-place mean of n floats (n % 4 == 0) over the ranks; bufs: DEVICE array [world] of every rank's peer-mapped buffer
+extern "C" int dexgg_grad_allreduce(const dexgg_slab_comm* q, void* const* bufs, long long n, float scale, int ctas, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(q && bufs && n >= 4 && n % 4 == 0, "grad_allreduce: bad arguments (n %lld)", n);
+    SlabComm c;
+    if (int rc = slab_comm(*q, 0, nullptr, 1, c)) return rc;
+    DEXGG_REQUIRE(c.world >= 2, "grad_allreduce: world %d (nothing to exchange)", c.world);
+    if (ctas <= 0) ctas = 64;
+    grad_allreduce_kernel<<<ctas, 256, 0, TF_ST>>>(c, reinterpret_cast<float4* const*>(bufs), n / 4, scale);
+    count_launches(1);
+    DEXGG_LAUNCH_OK("grad_allreduce_kernel");
     return DEXGG_OK;
 }
 

@@ -82,9 +82,12 @@ class _Net:
         self.Y = [torch.zeros((R, HID), **bf) for _ in range(nb)]
         self.stat1 = [torch.zeros((2, groups, INNER), **f32) for _ in range(nb)]  # [mean | invstd]
         self.stat2 = [torch.zeros((2, groups, HID), **f32) for _ in range(nb)]
-        self.GY = torch.zeros((R, HID), **bf)
+        # gradients wrt a block's second / first layer output: one buffer PER BLOCK, so that the weight-gradient GEMMs reading
+        # them can run on the network's side stream while the chain moves on to the next block (backward_blocks)
+        self.GY = [torch.zeros((R, HID), **bf) for _ in range(nb)]
         self.GH = torch.zeros((R, INNER), **bf)
-        self.G13 = torch.zeros((R, NCAT), **bf)
+        self.G13 = [torch.zeros((R, NCAT), **bf) for _ in range(nb)]
+        self.wstream = None
         self.gXT = [torch.zeros((R, TAILW), **bf)] + [torch.zeros((R, LDXT), **bf) for _ in range(nb - 1)]
         self.tail_stat = torch.zeros((groups, 2, TAILW), **f32)  # per group: mean | invstd of the tail columns
         # column sums of the first-layer output gradient (fc3 part) and the gradients of the [X | tail] weight columns: one flat
@@ -145,6 +148,22 @@ def _maps(kind, b, n_tail, Fin):
     return cmap, dmap
 
 
+class _DeviceFloats:
+    """A float32 device buffer this library allocated (cudaMalloc through dexgg_peer_alloc), exposed to torch by the CUDA array
+    interface; `owner` keeps the allocation alive as long as a tensor made from it is."""
+
+    def __init__(self, ptr, numel, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": "<f4", "data": (ptr, False), "version": 2, "strides": None}
+
+
+def _wrap_device_floats(ptr, numel, dev, owner=None):
+    with torch.cuda.device(dev):
+        t = torch.as_tensor(_DeviceFloats(ptr, numel, owner), device=dev)
+    assert t.data_ptr() == ptr and t.numel() == numel and t.dtype == torch.float32
+    return t
+
+
 class TrainEngine:
     def __init__(self, model, batch_rows):
         """model: dexgangrasp.DexGanGrasp wrapper in training mode; batch_rows: rows per rank."""
@@ -202,6 +221,10 @@ class TrainEngine:
         self.world = _world()
         self.rank = dist.get_rank() if self.world > 1 else 0
         self._setup_exchange()
+        self.grad_ctas = int(os.environ.get("DEXGG_GRAD_CTAS", "0"))
+        self.wgrad_streams = os.environ.get("DEXGG_WGRAD_STREAMS", "1") != "0"
+        self.two_chains = os.environ.get("DEXGG_TWO_CHAINS", "1") != "0"
+        self._setup_grad_exchange()
         self.scratch = torch.zeros((64 * self.SLOT,), **f32)
         self.bar = torch.zeros((4,), dtype=torch.int32, device=dev)
         self._slot = 0
@@ -238,12 +261,63 @@ class TrainEngine:
             if self.world > 1:
                 dist.barrier()  # every rank has mapped every scratch before anyone launches into it
 
+    def _setup_grad_exchange(self):
+        """Data parallel over the peer mapping: the three flat gradient buffers move into ONE peer-mapped allocation per rank, so
+        dexgg_grad_allreduce (two-shot over NVLink, one launch, in the step's own stream) replaces the NCCL gradient allreduce."""
+        self.grad_p2p = bool(self.p2p and self.world > 1 and os.environ.get("DEXGG_DP_GRADS", "p2p") != "nccl")
+        if not self.grad_p2p:
+            return
+        L = _L()
+        nets = (self.G, self.D, self.E)
+        sizes = [(n.flat_grad.numel() + 63) // 64 * 64 for n in nets]  # 256-byte aligned sub-buffers
+        with torch.cuda.device(self.dev):
+            mine, handle = ctypes.c_void_p(), (ctypes.c_ubyte * 64)()
+            _native.check(L.dexgg_peer_alloc(4 * sum(sizes), ctypes.byref(mine), handle))
+            self._grad_mine = mine
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(handle))
+            bases = []
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    bases.append(mine.value)
+                    continue
+                q = ctypes.c_void_p()
+                _native.check(L.dexgg_peer_open((ctypes.c_ubyte * 64).from_buffer_copy(h), ctypes.byref(q)))
+                self._peer_opened.append(q)
+                bases.append(q.value)
+            off = 0
+            for n, sz in zip(nets, sizes):
+                numel = n.flat_grad.numel()
+                n.flat_grad = _wrap_device_floats(mine.value + 4 * off, numel, self.dev, owner=self)
+                n.module._dexgg_flat_grad = n.flat_grad
+                n.grad_peers = torch.tensor([b + 4 * off for b in bases], dtype=torch.int64, device=self.dev)
+                n.attach()
+                off += sz
+            dist.barrier()
+
+    def sync_grads(self, net):
+        """Average `net`'s gradients over the ranks (dexgangrasp._sync_grads for the engine's flat buffers)."""
+        if self.world == 1:
+            return
+        if not self.grad_p2p:
+            self.model._sync_grads(net.module)
+            return
+        from . import dataparallel
+        c = SlabComm()
+        c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
+        self._pslot += 1
+        assert self._pslot <= 64
+        dataparallel._COUNTERS["p2p_calls"] = dataparallel._COUNTERS.get("p2p_calls", 0) + 1
+        dataparallel._COUNTERS["p2p_grad_bytes"] = dataparallel._COUNTERS.get("p2p_grad_bytes", 0) + 4 * net.flat_grad.numel()
+        _native.check(_L().dexgg_grad_allreduce(ctypes.byref(c), net.grad_peers.data_ptr(), net.flat_grad.numel(), 1.0 / self.world,
+                                                self.grad_ctas, _st(self.dev)))
+
     def _comm(self, a):
         c = a.comm
         from . import dataparallel
         c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
         self._pslot += 1
-        assert self._pslot <= 48
+        assert self._pslot <= 64
         if self.world > 1:
             dataparallel._COUNTERS["p2p_calls"] = dataparallel._COUNTERS.get("p2p_calls", 0) + 1
 
@@ -275,7 +349,7 @@ class TrainEngine:
         nb = (n + 2047) // 2048
         c.peers, c.world, c.rank, c.slot, c.parity = self.peer_table.data_ptr(), self.world, self.rank, self._pslot, self.parity.data_ptr()
         self._pslot += nb
-        assert self._pslot <= 48
+        assert self._pslot <= 64
         dataparallel._COUNTERS["p2p_calls"] = dataparallel._COUNTERS.get("p2p_calls", 0) + 1
         _native.check(_L().dexgg_p2p_small(ctypes.byref(c), src.data_ptr(), n, _native.ptr(sum_out), _native.ptr(gather_out), _st(self.dev)))
 
@@ -507,28 +581,51 @@ class TrainEngine:
         if want_wgrad:
             net.small_scratch.zero_()  # db13 of every block + the dWxt scratch of every block (split contractions accumulate)
         g_src = last
+        # The weight-gradient GEMMs (a third of the step's tensor-core time) are off the critical path: nothing in the backward
+        # chain reads them before `unfold`.  They go to the network's side stream behind an event, the chain continues with the
+        # data-gradient GEMM / the next slab kernel, and joins the side stream at the end.
+        cur = torch.cuda.current_stream(self.dev)
+        ws = None
+        if want_wgrad and self.wgrad_streams:
+            if net.wstream is None:
+                net.wstream = torch.cuda.Stream(self.dev)
+            ws = net.wstream
+
+        def off_chain(fn):
+            if ws is None:
+                fn()
+                return
+            ws.wait_stream(cur)
+            with torch.cuda.stream(ws):
+                fn()
+
         for b in range(nb - 1, -1, -1):
             blk, rb = net.blocks[b], net.blocks[b].rb
+            GY, G13 = net.GY[b], net.G13[b]
             out, ldo = (net.XT[b + 1], LDXT) if b + 1 < nb else (net.Xlast, HID)
             kw = dict(g=g_src[1].data_ptr(), ldg=g_src[2]) if g_src[0] == "mat" else dict(rank1=(g_src[1], g_src[2], g_src[3]))
-            self._bn_bwd(HID, rpg, groups, rb.bn2, net.stat2[b], net.Y[b].data_ptr(), HID, out.data_ptr(), ldo, net.GY.data_ptr(), HID,
-                         skip=net.T[b][:, INNER:].data_ptr(), lds=NCAT, gskip=net.G13[:, INNER:].data_ptr(), ldgs=NCAT,
+            self._bn_bwd(HID, rpg, groups, rb.bn2, net.stat2[b], net.Y[b].data_ptr(), HID, out.data_ptr(), ldo, GY.data_ptr(), HID,
+                         skip=net.T[b][:, INNER:].data_ptr(), lds=NCAT, gskip=G13[:, INNER:].data_ptr(), ldgs=NCAT,
                          dbias_skip=net.db13[b][INNER:].data_ptr(), want_wgrad=want_wgrad, drop=(drops[b] if drops else None), **kw)
             if want_wgrad:  # dW2 = GY^T . H  (both operands MN-major, contraction over the rows split over CTAs)
                 # [512 x 256] output, contraction over the rows: 64-column tiles x 8-way split = 128 CTAs, 8 atomic adds per element
-                self._gemm(HID, INNER, [(net.GY.data_ptr(), HID, 1, net.H[b].data_ptr(), INNER, 1, R)], C32=rb.fc2.weight.grad, ldc=INNER,
-                           split_k=max(1, min(8, R // 512)), tile_n=64)
-            self._gemm(R, INNER, [(net.GY.data_ptr(), HID, 0, blk.W2.data_ptr(), INNER, 1, HID)], C16=net.GH, ldc=INNER)
-            self._bn_bwd(INNER, rpg, groups, rb.bn1, net.stat1[b], net.T[b].data_ptr(), NCAT, net.H[b].data_ptr(), INNER, net.G13.data_ptr(), NCAT,
+                off_chain(lambda: self._gemm(HID, INNER, [(GY.data_ptr(), HID, 1, net.H[b].data_ptr(), INNER, 1, R)], C32=rb.fc2.weight.grad,
+                                             ldc=INNER, split_k=max(1, min(8, R // 512)), tile_n=64))
+            self._gemm(R, INNER, [(GY.data_ptr(), HID, 0, blk.W2.data_ptr(), INNER, 1, HID)], C16=net.GH, ldc=INNER)
+            self._bn_bwd(INNER, rpg, groups, rb.bn1, net.stat1[b], net.T[b].data_ptr(), NCAT, net.H[b].data_ptr(), INNER, G13.data_ptr(), NCAT,
                          g=net.GH.data_ptr(), ldg=INNER, want_wgrad=want_wgrad)
             xin, ldx, K2 = self._block_in(net, b)
             if want_wgrad:  # gradients wrt the folded first-layer weights: [768, 4096] and [768, X | tail]
-                self._gemm(NCAT, BPS, [(net.G13.data_ptr(), NCAT, 1, xhat.data_ptr(), BPS, 1, R)], C32=blk.dWb, ldc=BPS)
-                self._gemm(NCAT, blk.ldxt, [(net.G13.data_ptr(), NCAT, 1, xin.data_ptr(), ldx, 1, R)], C32=blk.dWxt, ldc=blk.ldxt,
-                           split_k=max(1, min(4 if blk.has_x else 16, R // 512)))
+                def first_layer_wgrads(G13=G13, blk=blk, xin=xin, ldx=ldx):
+                    self._gemm(NCAT, BPS, [(G13.data_ptr(), NCAT, 1, xhat.data_ptr(), BPS, 1, R)], C32=blk.dWb, ldc=BPS)
+                    self._gemm(NCAT, blk.ldxt, [(G13.data_ptr(), NCAT, 1, xin.data_ptr(), ldx, 1, R)], C32=blk.dWxt, ldc=blk.ldxt,
+                               split_k=max(1, min(4 if blk.has_x else 16, R // 512)))
+                off_chain(first_layer_wgrads)
             if b > 0 or want_tail_grad:
-                self._gemm(R, blk.ldxt, [(net.G13.data_ptr(), NCAT, 0, blk.Wxt.data_ptr(), blk.ldxt, 1, NCAT)], C16=net.gXT[b], ldc=blk.ldxt)
+                self._gemm(R, blk.ldxt, [(G13.data_ptr(), NCAT, 0, blk.Wxt.data_ptr(), blk.ldxt, 1, NCAT)], C16=net.gXT[b], ldc=blk.ldxt)
                 g_src = ("mat", net.gXT[b], blk.ldxt)
+        if ws is not None:
+            cur.wait_stream(ws)
 
     def _score_head(self, net, R, groups, targets=(0.0, 0.0), dscale=(0.0, 0.0), lscale=(0.0, 0.0), labels=None, loss_slot=0, want_db=True):
         a = ScoreHead()
@@ -652,11 +749,11 @@ class TrainEngine:
         with torch.cuda.device(dev), torch.no_grad():
             self._input_norm(d["bps_object"])
             self._gan_d_step(d, Zgen)
-            m._sync_grads(D.module)
+            self.sync_grads(D)
             D.optimizer.step()
             if is_train_gen:
                 self._gan_g_step(d)
-                m._sync_grads(G.module)
+                self.sync_grads(G)
                 G.optimizer.step()
             out, _ = self._gan_losses(is_train_gen)
         self._bump_versions(self.G, self.D)
@@ -694,7 +791,7 @@ class TrainEngine:
         with torch.cuda.device(dev), torch.no_grad():
             self._input_norm(d["bps_object"])
             self._eva_grads(d)
-            m._sync_grads(E.module)
+            self.sync_grads(E)
             E.optimizer.step()
             val = self.loss[6].clone()
             if self.world > 1:
@@ -725,23 +822,32 @@ class TrainEngine:
         if getattr(self, "_side_stream", None) is None:
             self._side_stream = torch.cuda.Stream(dev)
         side = self._side_stream
+        # Two spinning kernels (one per chain) must always fit the GPU together: true for the capped slab grids and the narrow
+        # gradient-exchange kernel, NOT for an NCCL kernel next to a slab grid - with NCCL gradients the chains run one after the other.
+        two_chains = self.two_chains and (self.world == 1 or self.grad_p2p)
         with torch.cuda.device(dev), torch.no_grad():
             self._input_norm(d["bps_object"])
-            self.slab_ctas = 1
+            if not two_chains:
+                self._eva_grads(d)
+                self.sync_grads(E)
+                E.optimizer.step()
+            self.slab_ctas = 1 if two_chains else 0
             try:
-                side.wait_stream(main)
-                with torch.cuda.stream(side):   # chain 2: the evaluator update
-                    self._eva_grads(d)
-                    m._sync_grads(E.module)
-                    E.optimizer.step()
+                if two_chains:
+                    side.wait_stream(main)
+                    with torch.cuda.stream(side):   # chain 2: the evaluator update
+                        self._eva_grads(d)
+                        self.sync_grads(E)
+                        E.optimizer.step()
                 self._gan_d_step(d, Zgen)      # chain 1: the GAN update
-                m._sync_grads(D.module)
+                self.sync_grads(D)
                 D.optimizer.step()
                 if is_train_gen:
                     self._gan_g_step(d)
-                    m._sync_grads(G.module)
+                    self.sync_grads(G)
                     G.optimizer.step()
-                main.wait_stream(side)
+                if two_chains:
+                    main.wait_stream(side)
             finally:
                 self.slab_ctas = 0
             out, vals = self._gan_losses(is_train_gen)

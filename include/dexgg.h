@@ -219,7 +219,7 @@ int dexgg_gemm_bf16(const dexgg_gemm* g, void* stream);
  * ranks of a data-parallel job INSIDE the kernel, through peer-mapped scratch buffers (cudaIpc over NVLink) - one exchange per
  * BatchNorm, no NCCL launch, bit-identical totals on every rank.  peers: DEVICE array [world] of every rank's scratch base
  * (dexgg_peer_alloc(dexgg_slab_scratch_bytes()) on each rank, handles exchanged by the host, dexgg_peer_open on the others);
- * slot: index of this launch inside the step (same on every rank, < 32); parity: device word flipped by dexgg_slab_step_begin
+ * slot: index of this launch inside the step (same on every rank, < 64); parity: device word flipped by dexgg_slab_step_begin
  * at the start of every step.  world = 1: peers = {own scratch}. */
 typedef struct {
     void* const* peers;
@@ -235,6 +235,13 @@ int dexgg_slab_step_begin(void* scratch_base, unsigned* parity, void* stream);
 /* small cross-rank sum (sum_out, may alias src) and / or gather (gather_out [world, n]) of n floats through the same peer scratch:
  * one launch, no NCCL; takes ceil(n / 2048) slots starting at comm->slot */
 int dexgg_p2p_small(const dexgg_slab_comm* comm, const float* src, int n, float* sum_out, float* gather_out, void* stream);
+/* gradient exchange of a data-parallel step without NCCL: in-place MEAN (scale = 1 / world) of n floats (n % 4 == 0) held by
+ * every rank in peer-mapped memory (dexgg_peer_alloc + dexgg_peer_open; bufs: DEVICE array [world], bufs[rank] = own buffer).
+ * Two-shot over NVLink: rank r reduces chunk r of every rank in rank order and stores the result to every rank, so the ranks
+ * end bit-identical.  One launch of `ctas` (0: 64) narrow CTAs, one exchange slot (comm->slot) for its two flag barriers.
+ * Replaces dataparallel.allreduce_gradients' NCCL call for the training engine (reference: single-process training,
+ * train.py:249-276; the data-parallel step is this repo's multi-GPU row e2). */
+int dexgg_grad_allreduce(const dexgg_slab_comm* comm, void* const* bufs, long long n, float scale, int ctas, void* stream);
 
 /* Train-mode BatchNorm1d forward as ONE kernel: batch statistics of x per group of rows_per_group rows (the discriminator's
  * real and fake batches are two groups of one call), y = [dropout] LeakyReLU(gamma * xhat + beta [+ residual]).  A CTA owns

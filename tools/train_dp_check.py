@@ -20,12 +20,15 @@ dev = torch.device("cuda", local)
 B = int(os.environ.get("DP_BATCH", "512"))
 prec = os.environ.get("DEXGG_PRECISION", "fp32")
 graph = os.environ.get("DP_GRAPH", "0") == "1"
+combined = os.environ.get("DP_COMBINED", "0") == "1"  # GAN + evaluator update per step (TrainEngine.combined_step: two chains)
 
 
 def fresh():
     m = DexGanGrasp(dict(bench.TRAIN_CFG, gpu_ids=[local], precision=prec))
     m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(7))
     m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(7))
+    if combined:
+        m.DexEvaluator.dout.p = 0.0  # the dropout stream is per local row: switched off so that sharded == full batch
     return m
 
 
@@ -34,6 +37,8 @@ z = synth.synth_latents(B, 5, seed=3)
 ref = fresh()
 for _ in range(2 if graph else 1):
     lg = ref.update_dexgangrasp({k: v.to(dev) for k, v in full.items()}, is_train_gen=True, Zgen=z.to(dev))
+    if combined:
+        lg = dict(lg, **ref.update_dexevaluator({k: v.to(dev) for k, v in full.items()}))
 torch.cuda.synchronize()
 
 dist.init_process_group("nccl", device_id=dev)
@@ -44,12 +49,15 @@ zmine = z[rank * n:(rank + 1) * n].to(dev)
 cap = None
 if graph:
     from dex_gan_grasp_b200.graph_step import CapturedTrainStep
-    cap = CapturedTrainStep(dp, mine, with_evaluator=False, is_train_gen=True, warmup=1, example_z=zmine)
+    cap = CapturedTrainStep(dp, mine, with_evaluator=combined, is_train_gen=True, warmup=1, example_z=zmine)
     lg2 = cap(mine, z=zmine)
 else:
     lg2 = dp.update_dexgangrasp(mine, is_train_gen=True, Zgen=zmine)
+    if combined:
+        lg2 = dict(lg2, **dp.update_dexevaluator(mine))
 torch.cuda.synchronize()
-out = {"world": world, "batch": B, "precision": prec, "captured_graph": graph, "loss_abs_diff": {}, "max_weight_diff": 0.0, "max_buffer_diff": 0.0}
+out = {"world": world, "batch": B, "precision": prec, "captured_graph": graph, "combined": combined,
+       "engine": dp.train_engine_name(), "collectives": dataparallel.collective_counters(), "loss_abs_diff": {}, "max_weight_diff": 0.0, "max_buffer_diff": 0.0}
 for k in lg:
     # per-rank losses are means over the local shard: average them over ranks to compare with the full-batch mean
     t = torch.tensor([float(lg2[k])], device=dev, dtype=torch.float64)
@@ -57,6 +65,10 @@ for k in lg:
     out["loss_abs_diff"][k] = abs(float(t) / world - float(lg[k]))
 params = {k for k, _ in ref.DexGANGrasp.named_parameters()}
 sd_a, sd_b = ref.DexGANGrasp.state_dict(), dp.DexGANGrasp.state_dict()
+if combined:
+    params |= {"eva." + k for k, _ in ref.DexEvaluator.named_parameters()}
+    sd_a = dict(sd_a, **{"eva." + k: v for k, v in ref.DexEvaluator.state_dict().items()})
+    sd_b = dict(sd_b, **{"eva." + k: v for k, v in dp.DexEvaluator.state_dict().items()})
 for k in sd_a:
     if not sd_a[k].is_floating_point():
         continue
@@ -74,7 +86,7 @@ for k in ga:
         worst = max(worst, (float((ga[k].grad.double() - gb[k].grad.double()).norm()) / den, k))
 out["worst_grad_rel_diff"] = worst
 # weights must be identical on every rank after the step
-flat = torch.cat([p.detach().reshape(-1) for p in dp.DexGANGrasp.parameters()])
+flat = torch.cat([p.detach().reshape(-1) for p in list(dp.DexGANGrasp.parameters()) + list(dp.DexEvaluator.parameters())])
 mx, mn = flat.clone(), flat.clone()
 dist.all_reduce(mx, op=dist.ReduceOp.MAX)
 dist.all_reduce(mn, op=dist.ReduceOp.MIN)
