@@ -608,11 +608,19 @@ __global__ void __launch_bounds__(256) fp32_probe_kernel(int iters, float* out) 
 
 }  // namespace dexgg
 
+namespace dexgg {
+int bps_umma_launch(const float* basis, int P, const float* pts, const int64_t* offsets, int B, int64_t uniform_n, int64_t total,
+                    int nsplit, unsigned long long* keys, void* extra, cudaStream_t st);  // bps_umma.cu
+size_t bps_umma_extra_bytes(int P);
+int bps_umma_basis_per_cta();
+int bps_umma_ctas_per_sm();
+}
+
 using namespace dexgg;
 
 extern "C" size_t dexgg_bps_workspace_bytes(int B, int P) {
     if (B < 0 || P < 0) return 0;
-    return align_up((size_t)B * (size_t)P * sizeof(unsigned long long), 256);
+    return align_up((size_t)B * (size_t)P * sizeof(unsigned long long), 256) + bps_umma_extra_bytes(P);
 }
 
 template <int R>
@@ -662,6 +670,31 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
             dim3 grid((P + 127) / 128, B);
             bps_nn_scalar_kernel<<<grid, 128, 0, st>>>(basis, P, pts, offsets, max_cloud_points, keys); ::dexgg::count_launches(1);
             DEXGG_LAUNCH_OK("bps_nn_scalar_kernel");
+        } else if (!(flags & (DEXGG_BPS_DIRECT | DEXGG_BPS_FMA))) {
+            // default: the filter scan on the tensor cores (bps_umma.cu), 512 basis points x one point range per CTA, two CTAs per
+            // SM.  Splits of the point range (merged by atomicMin): enough CTAs to fill the GPU when there are few clouds (the
+            // online one-object shape, dexgangrasp_real_robot.py:139), and ranges of at most 2048 points, which stay resident in
+            // shared memory for the exact pass; never below 512 points per split.
+            const int gx = (P + bps_umma_basis_per_cta() - 1) / bps_umma_basis_per_cta();
+            int nsplit = (flags >> 8) & 0xff;
+            if (nsplit == 0) {
+                const int64_t have = (int64_t)gx * B, slots = (int64_t)bps_umma_ctas_per_sm() * sm_count();
+                int64_t s = (max_cloud_points + 2047) / 2048;
+                if (have * s < slots) s = (slots + have - 1) / have;
+                const int64_t smax = (max_cloud_points + 511) / 512;
+                if (s > smax) s = smax;
+                if (s < 1) s = 1;
+                if (s > 4096) s = 4096;
+                nsplit = (int)s;
+            }
+            if ((max_cloud_points + nsplit - 1) / nsplit + 8 > (int64_t)65536 * 32) {  // 16-bit chunk ids
+                int rc = launch_packed<16>(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys, st);
+                if (rc != DEXGG_OK) return rc;
+            } else {
+                int rc = bps_umma_launch(basis, P, pts, offsets, B, max_cloud_points, total_points, nsplit, keys,
+                                         static_cast<unsigned char*>(workspace) + align_up((size_t)B * P * sizeof(unsigned long long), 256), st);
+                if (rc != DEXGG_OK) return rc;
+            }
         } else {
             // basis points per thread: 8 for the filter kernel (94 registers -> 5 CTAs / 20 warps per SM; measured 1.52 ms at C3
             // against 1.65 ms for 16 and 1.55 ms for 4), 16 for the direct kernel as tuned in round 1

@@ -61,6 +61,8 @@ unsigned long long dexgg_launch_count(void);
 #define DEXGG_BPS_SCALAR 1     /* simple scalar compare-select kernel (cross-check of the packed kernels) */
 #define DEXGG_BPS_DIRECT 2     /* packed kernel that scans with the direct-difference form itself (6 FP32 ops / pair) instead of
                                   the default expanded-form filter (3 FFMA / pair) + exact evaluation of the candidates */
+#define DEXGG_BPS_FMA 4        /* the filter scan on the FP32 pipe (bps_nn_filter_kernel, 3 FFMA / pair) instead of the default
+                                  tensor-core scan (bps_umma.cu); same results, kept as its cross-check */
 #define DEXGG_BPS_NSPLIT(n) (((n) & 0xff) << 8) /* force the number of point-range splits per cloud (0 = auto) */
 
 size_t dexgg_bps_workspace_bytes(int B, int P);

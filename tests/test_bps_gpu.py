@@ -11,6 +11,7 @@ pytestmark = pytest.mark.gpu
 NSPLIT = lambda n: (n & 0xff) << 8
 SCALAR = 1
 DIRECT = 2  # direct-difference scan instead of the default expanded-form filter + exact candidates
+FMA = 4     # the filter scan on the FP32 pipe instead of the default tensor-core scan
 
 
 def dev_encode(basis, clouds, flags=0):
@@ -25,7 +26,7 @@ def dev_encode(basis, clouds, flags=0):
     return d.cpu().numpy(), i.cpu().numpy()
 
 
-@pytest.mark.parametrize("flags", [0, SCALAR, NSPLIT(3), DIRECT, DIRECT | NSPLIT(2)])
+@pytest.mark.parametrize("flags", [0, SCALAR, NSPLIT(3), DIRECT, DIRECT | NSPLIT(2), FMA, FMA | NSPLIT(3)])
 def test_reference_fixtures_bit_exact(bps_golden, flags):
     basis = bps_golden["basis"]
     names = list(bps_golden["names"])
@@ -49,7 +50,7 @@ def test_encoder_class_surface(bps_golden):
     assert torch.allclose(r["deltas"].norm(dim=2), r["dists"], atol=1e-7)
 
 
-@pytest.mark.parametrize("flags", [0, NSPLIT(2), NSPLIT(5), SCALAR, DIRECT, DIRECT | NSPLIT(5)])
+@pytest.mark.parametrize("flags", [0, NSPLIT(2), NSPLIT(5), SCALAR, DIRECT, DIRECT | NSPLIT(5), FMA, FMA | NSPLIT(5)])
 def test_ragged_random_vs_oracle(oracle_lib, bps_golden, flags):
     rng = np.random.default_rng(3)
     basis = bps_golden["basis"]
@@ -67,7 +68,7 @@ def test_ties_duplicates_lowest_index(oracle_lib):
     basis = rng.uniform(-0.2, 0.2, (300, 3)).astype(np.float32)  # P not a multiple of anything
     base = (rng.integers(-8, 8, (40, 3)) / 64.0).astype(np.float32)  # coarse grid -> many exact ties
     cloud = base[rng.integers(0, 40, 3000)]
-    for flags in (0, NSPLIT(4), SCALAR, DIRECT):
+    for flags in (0, NSPLIT(4), SCALAR, DIRECT, FMA):
         d, i = dev_encode(basis, [cloud, cloud[::-1].copy()], flags)
         for b, c in enumerate([cloud, cloud[::-1].copy()]):
             do, io = oracle_bps(oracle_lib, basis, c)
@@ -90,7 +91,7 @@ def test_filter_near_ties_and_off_centre_clouds(oracle_lib, bps_golden):
     huge = (rng.normal(0, 30.0, (3000, 3))).astype(np.float32)
     onb = np.concatenate([basis[::3], rng.normal(0, 0.1, (1000, 3)).astype(np.float32)])
     clouds = [shell, tiny, far, huge, onb]
-    for flags in (0, NSPLIT(3)):
+    for flags in (0, NSPLIT(3), FMA):
         d, i = dev_encode(basis, clouds, flags)
         for b, c in enumerate(clouds):
             do, io = oracle_bps(oracle_lib, basis, c)
@@ -113,7 +114,7 @@ def test_shared_memory_finish_small_ranges(oracle_lib, bps_golden):
     clouds = [grid[rng.integers(0, 30, 2047)], shell, far, rng.normal(0, 0.08, (1, 3)).astype(np.float32),
               rng.normal(0, 0.08, (33, 3)).astype(np.float32), rng.normal(0, 0.08, (1023, 3)).astype(np.float32),
               rng.normal(0, 0.08, (1025, 3)).astype(np.float32), rng.normal(0, 0.08, (2048, 3)).astype(np.float32)]
-    for flags in (0, NSPLIT(2)):
+    for flags in (0, NSPLIT(2), FMA):
         d, i = dev_encode(basis, clouds, flags)
         for b, c in enumerate(clouds):
             do, io = oracle_bps(oracle_lib, basis, c)
