@@ -668,13 +668,24 @@ def main():
         roof = {"bound": "fp32", "kernel": "linear_simt_kernel (fp32 CUDA-core mode, all MLP layers)", "achieved": mlp_tflops,
                 "peak": fp32_tflops, "unit": "TFLOP/s", "frac": mlp_tflops / fp32_tflops,
                 "peak_source": "FFMA probe measured in this run (dexgg_fp32_pipe_probe)", "traffic": None}
-    roof["bps_kernel"] = {"bound": "fp32", "kernel": "bps_nn_filter_kernel (expanded-form filter scan + exact direct-form candidates)",
-                          "achieved": bps_lane_tops, "peak": fp32_tflops / 2,
-                          "unit": "T lane-op/s (3 FFMA per pair executed by the scan)", "frac": bps_lane_tops / (fp32_tflops / 2),
+    # BPS (second kernel of the step): the filter scan runs on the tensor cores and is read out of TMEM with one 3-input min per two
+    # (basis, point) pairs: its bound is the ALU pipe (FMNMX3), measured live by the library's probe (kind 3: dependent FMNMX3 chains)
+    ms_alu, ops_alu = ctypes.c_float(), ctypes.c_double()
+    _native.check(L.dexgg_fp32_pipe_probe(3, 2000, ctypes.byref(ms_alu), ctypes.byref(ops_alu)))
+    alu_tops = ops_alu.value / (ms_alu.value * 1e-3) / 1e12  # T lane-op/s of the ALU pipe on this GPU
+    bps_alu_tops = 0.5 * bps_pairs / (t_bps * 1e-3) / 1e12   # algorithmic: one FMNMX3 lane-op per two pairs
+    roof["bps_kernel"] = {"bound": "alu", "kernel": "bps_nn_umma_kernel (a() = |x|^2 - 2 b.x by tcgen05 K = 32 split-bf16 MMAs, min scan out of "
+                                                    "TMEM, exact direct-form pass on the candidate chunks)",
+                          "achieved": bps_alu_tops, "peak": alu_tops,
+                          "unit": "T lane-op/s (ALGORITHMIC: one FMNMX3 per two pairs; the scan executes ~0.75 ALU lane-ops per pair "
+                                  "with the candidate rule)", "frac": bps_alu_tops / alu_tops,
                           "pairs_per_s": bps_pairs / (t_bps * 1e-3),
-                          "note": "frac = EXECUTED FP32-pipe lane-ops / FFMA probe peak.  (A direct-difference scan needs 6 lane-ops per "
-                                  "pair - SURVEY 8d - so the same pairs/s would be 2x this fraction of the pipe for that algorithm; "
-                                  "that figure is an algorithm comparison, not a utilisation.)"}
+                          "fp32_pipe_equivalent": {"lane_tops_if_3_ffma_per_pair": bps_lane_tops, "ffma_peak": fp32_tflops / 2,
+                                                   "frac": bps_lane_tops / (fp32_tflops / 2),
+                                                   "note": "what the FP32-pipe filter kernel (flag DEXGG_BPS_FMA, r02j: 0.63) would need "
+                                                           "for the same pairs/s; > its measured fraction = the gain of the tensor-core scan"},
+                          "note": "stage time includes memset + basis pack + finish kernels; profiles/r02n_bps_umma_ncu_full.md holds the pipe "
+                                  "utilisation of the kernel alone"}
 
     # ---- max over ranks ----
     t = torch.tensor([ms, ms_e2e, ms_e2e_sync, st_dev["p90"]], device=dev, dtype=torch.float64)

@@ -18,14 +18,15 @@
 //   The candidate rule and its margin are those of bps_nn_filter_kernel with this E.
 //
 // The epilogue reads a() from TMEM (thread = TMEM lane = basis point, 32 columns = one chunk per tcgen05.ld) and needs ONE
-// FMNMX3 per two pairs + ~12 ALU operations per chunk: the scan is bound by the ALU pipe (min / select), ~75 pairs / clk / SM
+// FMNMX3 per two pairs + ~8 ALU operations per chunk: the scan is bound by the ALU pipe (min / select, 64 lanes / clk / SM)
 // against 128 / 3 = 43 for the FFMA form.
 //
-// CTA = 21 warps: four scan groups of four warps (group g owns the 128-column accumulator g and the M blocks 4j + g; the four
-// warps of an SMSP belong to four different groups, so one group's wait for its MMA is covered by the scans of the others),
-// four converter warps, which turn the raw AoS tile (TMA bulk copy, as it lies in HBM) into the B operand (64-byte swizzle,
-// K-major) of the NEXT tile while the current one is scanned, and the MMA issuer.  1024 basis points per CTA stay resident as
-// the A operand (packed once per call by bps_basis_pack_kernel, one bulk copy per CTA).
+// CTA (two per SM) = 11 warps over 512 basis points: two scan groups of four warps (group g owns one 128-column accumulator
+// and the M blocks 2j + g; the four scan warps of an SMSP belong to four different groups of the two resident CTAs, so one
+// group's wait for its MMA is covered by the scans of the others), two converter warps, which turn the raw AoS tile (TMA bulk
+// copy, as it lies in HBM) into the B operand (64-byte swizzle, K-major) of the NEXT tile while the current one is scanned, and
+// the MMA issuer.  The basis points stay resident as the A operand (packed once per call by bps_basis_pack_kernel, one bulk
+// copy per CTA).  BU_CFG 0 is the one-CTA-per-SM layout (1024 basis points, four groups): measured 10 % slower.
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
