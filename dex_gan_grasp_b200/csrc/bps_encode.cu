@@ -734,6 +734,41 @@ extern "C" int dexgg_bps_encode(const float* basis, int P, const float* pts, con
     return DEXGG_OK;
 }
 
+// ---- allocation-free variant: the workspace is a file-scope device array (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  Every GPU that loads the library holds the array until exit.  In HOST code the array's name is only a stand-in for
+// the symbol, not a device address: the address is asked for once per device, with that device current (cudaGetSymbolAddress), and
+// that pointer is what the kernels get.  All calls on a device share the array and it keeps the previous call's contents: the keys
+// and the basis norms are re-initialised in stream order by every call (dexgg_bps_encode does that for any workspace); two calls
+// that overlap on the GPU (different streams without an ordering between them) race on it.
+constexpr size_t BPS_STATIC_MAX_KEYS = 64 * 4096;  // B * P of one call: e.g. 64 clouds x the reference's 4096 basis points
+constexpr size_t BPS_STATIC_BYTES = BPS_STATIC_MAX_KEYS * sizeof(unsigned long long) + (512u << 10);  // + packed basis operand, norms
+static __device__ __align__(256) unsigned char bps_static_scratch[BPS_STATIC_BYTES];
+
+extern "C" size_t dexgg_bps_encode_static_max_keys(void) { return BPS_STATIC_MAX_KEYS; }
+
+extern "C" int dexgg_bps_encode_static(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
+                                       int64_t max_cloud_points, int64_t total_points, float* dists, int32_t* idx, int flags,
+                                       void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(P >= 1 && B >= 0, "bps_encode_static: bad sizes P=%d B=%d", P, B);
+    const size_t need = dexgg_bps_workspace_bytes(B, P);
+    DEXGG_REQUIRE((size_t)B * (size_t)P <= BPS_STATIC_MAX_KEYS && need <= BPS_STATIC_BYTES,
+                  "bps_encode_static: B * P = %zu exceeds the built-in scratch (at most %zu keys, %zu bytes; this call needs %zu bytes): "
+                  "use dexgg_bps_encode with a caller workspace", (size_t)B * (size_t)P, BPS_STATIC_MAX_KEYS, BPS_STATIC_BYTES, need);
+    static std::atomic<void*> dev_ptr[64];  // per device: the array's DEVICE address
+    int dev = 0;
+    DEXGG_CUDA_OK(cudaGetDevice(&dev));
+    DEXGG_REQUIRE(dev >= 0 && dev < 64, "bps_encode_static: device ordinal %d not supported", dev);
+    void* ws = dev_ptr[dev].load(std::memory_order_acquire);
+    if (!ws) {
+        DEXGG_CUDA_OK(cudaGetSymbolAddress(&ws, bps_static_scratch));
+        DEXGG_REQUIRE(ws != nullptr, "bps_encode_static: cudaGetSymbolAddress returned a null address");
+        dev_ptr[dev].store(ws, std::memory_order_release);
+    }
+    return dexgg_bps_encode(basis, P, pts, offsets, B, max_cloud_points, total_points, dists, idx, flags, ws, BPS_STATIC_BYTES, stream);
+}
+
 extern "C" int dexgg_bps_encode_host(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
                                      float* dists, int32_t* idx, int flags) {
     DEXGG_ARCH_OK();

@@ -69,6 +69,17 @@ size_t dexgg_bps_workspace_bytes(int B, int P);
 int dexgg_bps_encode(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
                      int64_t max_cloud_points, int64_t total_points, float* dists, int32_t* idx, int flags,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* dexgg_bps_encode WITHOUT a caller workspace and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The scratch (arg-min keys, packed basis operand) is a static device array inside the library, held by every GPU that
+ * loads it until exit (2.5 MiB).  Limit: B * P <= dexgg_bps_encode_static_max_keys() = 262144 (e.g. 64 clouds x 4096 basis points);
+ * beyond it the call fails with DEXGG_E_ARG and a message, and dexgg_bps_encode with a caller workspace is the path.  Same arguments,
+ * results (bit-identical) and flags otherwise.  The call itself calls no cudaMalloc / cudaFree.  All calls on a device SHARE the
+ * array: each call re-initialises what it needs in stream order, so calls ordered on one stream (or by events) are safe; calls that
+ * overlap on the GPU race on it. */
+size_t dexgg_bps_encode_static_max_keys(void);
+int dexgg_bps_encode_static(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
+                            int64_t max_cloud_points, int64_t total_points, float* dists, int32_t* idx, int flags, void* stream);
 /* Same call with HOST buffers (copies in, encodes, copies back, synchronises): the shape of
  * BPSEncoder.encode_pcd_with_bps (bps_encoder.py:28-55), which hands back a numpy array. offsets is a HOST array. */
 int dexgg_bps_encode_host(const float* basis, int P, const float* pts, const int64_t* offsets, int B, float* dists,
