@@ -1,12 +1,12 @@
 // Fused whole-network tcgen05 kernel for the DexGenerator / DexEvaluator forwards (eval-mode BatchNorm, hoisted BPS
 // projection).  See chain.cuh for the interface and DESIGN.md §4 for the roofline.
 //
-// One persistent CTA per SM, 320 threads, one 128-grasp tile at a time:
+// One persistent CTA per SM, 64 + 128 x CH_PARTS threads, one 128-grasp tile at a time:
 //   warp 0      weight producer: walks the pre-swizzled weight tile stream (built once by chain_pack) with 1-D bulk TMA
 //               copies into a 4-stage x 16 KB shared-memory ring (mbarrier expect_tx / complete_tx)
 //   warp 1      MMA issuer: one thread issues tcgen05.mma.kind::f16 (M=128, N=256, K=16); A = activation k-blocks resident
 //               in shared memory (9 slots x [128 rows x 64 bf16], 128B swizzle), B = ring stage, D = TMEM
-//   warps 2..9  epilogue: tcgen05.ld -> per-object base + BatchNorm affine + LeakyReLU -> bf16 -> next layer's A operand in
+//   warps 2..   epilogue (4 x CH_PARTS warps): tcgen05.ld -> per-object base + BatchNorm affine + LeakyReLU -> bf16 -> next layer's A operand in
 //               shared memory (or packed back into TMEM with tcgen05.st for the residual branch)
 // Per ResBlock (ResBlock.forward, networks.py:43-56), with X the 512-wide input (slots 0..7) and t the tail k-block (slot 8):
 //   P1  D[0,512)   = [X|t] . W3^T                         fc3 (skip branch), 2 x N=256 per k-block
@@ -23,10 +23,17 @@
 
 namespace dexgg {
 
-constexpr int CH_SLOT_BYTES = 16384, CH_NSLOT = 9, CH_STAGES = 4, CH_THREADS = 320, CH_HEAD_TILES = 8;
-constexpr int CH_PARAM_FLOATS = 2 * 768 + 512;  // per block: hoisted base of the tile's (at most) two objects + sh2
+#define CH_PARTS 4  // epilogue warps per TMEM lane quarter (four per SMSP); 2 software-pipelined ones (round 1) measured the same
+constexpr int CH_SLOT_BYTES = 16384, CH_NSLOT = 9, CH_STAGES = 4, CH_EPI_THREADS = 128 * CH_PARTS, CH_THREADS = 64 + CH_EPI_THREADS, CH_HEAD_TILES = 8;
+constexpr int CH_PARAM_FLOATS = 512;             // per block: sh2
+constexpr int CH_BASE_ROWS = 512, CH_BASE_BYTES = CH_BASE_ROWS * 32;  // hoisted per-object base of one phase as a B operand: [rows x 16 bf16]
 constexpr int CH_A_BYTES = CH_NSLOT * CH_SLOT_BYTES;
-constexpr int CH_SMEM_BYTES = CH_A_BYTES + CH_STAGES * CH_SLOT_BYTES + CH_PARAM_FLOATS * 4 + 256 + 1024;
+// 227 KB per CTA: the alignment slack is what is left (the dynamic window starts 1024-aligned when the kernel has no static shared
+// memory; the kernel traps if the slack does not cover the offset it finds)
+constexpr int CH_BAR_BYTES = 128;
+constexpr int CH_SMEM_USED = CH_A_BYTES + CH_STAGES * CH_SLOT_BYTES + CH_BASE_BYTES + CH_BAR_BYTES + CH_PARAM_FLOATS * 4;
+constexpr int CH_SMEM_BYTES = 227 * 1024;
+static_assert(CH_SMEM_USED <= CH_SMEM_BYTES, "shared memory budget");
 constexpr int CH_TAIL_SLOT = 8;
 #ifdef DEXGG_DEBUG
 constexpr bool CH_DEBUG = true;   // the DEXGG_CHAIN_NOSTREAM / DEXGG_CHAIN_CLOCKS experiments of DESIGN.md §4.2
@@ -118,6 +125,25 @@ __device__ __forceinline__ uint32_t lrelu_pack2(uint32_t a0, uint32_t a1, float 
     unpack2(x, x0, x1);
     return lrelu_bf16x2(pack_bf16x2(x0, x1));
 }
+// the same without an addend (the per-object base is accumulated by the tensor core)
+__device__ __forceinline__ uint32_t lrelu_cvt2(uint32_t a0, uint32_t a1) {
+    return lrelu_bf16x2(pack_bf16x2(__uint_as_float(a0), __uint_as_float(a1)));
+}
+// accumulator + bf16x2-packed residual only (the shift is accumulated by the tensor core)
+__device__ __forceinline__ uint32_t lrelu_res2(uint32_t a0, uint32_t a1, uint32_t r2) {
+    const f32x2 x = add2(pack2(__uint_as_float(a0), __uint_as_float(a1)), pack2(__uint_as_float(r2 << 16), __uint_as_float(r2 & 0xffff0000u)));
+    float x0, x1;
+    unpack2(x, x0, x1);
+    return lrelu_bf16x2(pack_bf16x2(x0, x1));
+}
+// v = p0 + p1 + p2 (bf16 each) up to 2^-24 |v|
+__device__ __forceinline__ void ch_split3(float v, uint32_t (&p)[3]) {
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(v);
+    const float r1 = v - __bfloat162float(h0);
+    const __nv_bfloat16 h1 = __float2bfloat16_rn(r1);
+    const __nv_bfloat16 h2 = __float2bfloat16_rn(r1 - __bfloat162float(h1));
+    p[0] = __bfloat16_as_ushort(h0); p[1] = __bfloat16_as_ushort(h1); p[2] = __bfloat16_as_ushort(h2);
+}
 // same with a third, bf16x2-packed addend (the residual branch)
 __device__ __forceinline__ uint32_t lrelu_pack3(uint32_t a0, uint32_t a1, float b0, float b1, uint32_t r2) {
     f32x2 x = add2(pack2(__uint_as_float(a0), __uint_as_float(a1)), pack2(b0, b1));
@@ -157,13 +183,16 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
     unsigned char* smem = ch_smem_raw + ((1024u - (smem_u32(ch_smem_raw) & 1023u)) & 1023u);
     unsigned char* sA = smem;                 // 9 activation k-block slots
     unsigned char* sR = smem + CH_A_BYTES;    // weight ring
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sR + CH_STAGES * CH_SLOT_BYTES);
+    unsigned char* sBase = sR + CH_STAGES * CH_SLOT_BYTES;  // base B-operand tile (32-byte swizzle)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sBase + CH_BASE_BYTES);
     uint64_t* full = bars;                    // [STAGES]
     uint64_t* empty = bars + CH_STAGES;       // [STAGES]
     uint64_t* mma_bar = bars + 2 * CH_STAGES; // MMA phase complete -> epilogue
     uint64_t* epi_bar = mma_bar + 1;          // epilogue phase complete (8 warps) -> MMA issuer
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(epi_bar + 1);
-    float* s_par = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(bars) + 256);  // [CH_PARAM_FLOATS]
+    uint64_t* base_bar = epi_bar + 1;         // base tile written (all epilogue warps) -> MMA issuer
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(base_bar + 1);
+    float* s_par = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(bars) + CH_BAR_BYTES);  // [CH_PARAM_FLOATS]
+    if ((int)(smem - ch_smem_raw) + CH_SMEM_USED > CH_SMEM_BYTES) __trap();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ntiles = (int)((a.M + 127) / 128);
@@ -178,7 +207,8 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             mbar_init(&empty[s], 1);
         }
         mbar_init(mma_bar, 1);
-        mbar_init(epi_bar, 8);
+        mbar_init(epi_bar, 4 * CH_PARTS);
+        mbar_init(base_bar, 4 * CH_PARTS);
         mbar_fence_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -256,19 +286,42 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                     if (++stage == CH_STAGES) { stage = 0; phase ^= 1; }
                 }
             };
+            // The per-object base of fc3 / fc1 (the hoisted BPS projection, fp32) is accumulated by the tensor core itself: the tail
+            // k-block carries one-hot columns 48..53 "row belongs to the tile's first / second object" (three each), and the epilogue
+            // warps write base[obj0 | obj1] of the phase's output columns as three bf16 parts each into a [rows x 16] B tile: one
+            // K = 16 MMA per N = 256 adds it exactly to 2^-24 - no base loads, no fp32 adds in the epilogue.  The bn2 shift of fc2
+            // goes the same way (its three parts in the slots of BOTH objects: the two one-hot groups sum to one).
+            const uint64_t ad_ind = umma_desc_sw128_kmajor(sA_u + CH_TAIL_SLOT * CH_SLOT_BYTES) + 6;
+            const uint32_t sB_u = smem_u32(sBase);
+            int bphase = 0;
+            auto base_mma = [&](bool staged, bool fresh, int ngroups, int row0, uint32_t d_col) {
+                if (fresh) {  // a new tile was written for this phase
+                    mbar_wait(base_bar, bphase);
+                    bphase ^= 1;
+                    tc_fence_after();
+                }
+                if (staged)
+                    for (int q = 0; q < ngroups; ++q)
+                        umma_bf16(tmem_base + d_col + q * 256, ad_ind, umma_desc_sw32_kmajor(sB_u + (row0 + q * 256) * 32), idesc256, 1u);
+            };
             for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+                const int64_t m_last = ((int64_t)t * 128 + 127 < a.M) ? (int64_t)t * 128 + 127 : a.M - 1;
+                const bool staged = (m_last / a.rows_per_obj) - ((int64_t)t * 128) / a.rows_per_obj <= 1;  // at most two objects
                 for (int b = 0; b < a.n_blocks; ++b) {
                     const int nkb = a.has_x[b] ? 9 : 1, s0 = a.has_x[b] ? 0 : CH_TAIL_SLOT;
                     wait_epi();  // P1: fc3 -> D[0,512)
                     for (int i = 0; i < nkb; ++i)
                         for (int q = 0; q < 2; ++q) mma_tile2(q * 256, s0 + i, i == 0);
+                    base_mma(staged, true, 2, 0, 0);
                     umma_commit(mma_bar); dbg();
                     wait_epi();  // P2: fc1 -> D[128,384)
                     for (int i = 0; i < nkb; ++i) mma_tile2(128, s0 + i, i == 0);
+                    base_mma(staged, true, 1, 0, 128);
                     umma_commit(mma_bar); dbg();
                     for (int h = 0; h < 2; ++h) {  // P3 / P4: fc2 halves -> D[128,384), A = H in slots 0..3
                         wait_epi();
                         for (int kb = 0; kb < 4; ++kb) mma_tile2(128, kb, kb == 0);
+                        base_mma(staged, h == 0, 1, h * 256, 128);  // + sh2 (the bn2 shift): same tile form, both one-hot slots
                         umma_commit(mma_bar); dbg();
                     }
                 }
@@ -292,13 +345,13 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
         }
     } else {
         // ===================== epilogue warps =====================
-        const int quarter = warp & 3, half = (warp - 2) >> 2;
+        const int quarter = warp & 3, part = (warp - 2) >> 2;  // TMEM lanes 32 * (warp % 4) ..; `part`: which share of a phase's columns
+        const int half = part >> 1;  // which 256-column half of the fc3 accumulator
         const int row = quarter * 32 + lane;
         const int etid = threadIdx.x - 64;  // 0..255 among the epilogue threads
         const uint32_t tlane = tmem_base + ((uint32_t)(quarter * 32) << 16);
         const int64_t ldbase = 768 * (int64_t)a.n_blocks;
-        float* s_base = s_par;               // [2][768] hoisted base of the tile's first / second object
-        float* s_sh2 = s_par + 2 * 768;      // [512]
+        float* s_sh2 = s_par;                // [512]
         int mphase = 0;
         int dbg_n = 0;
         auto dbg = [&]() {
@@ -317,7 +370,7 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             __syncwarp();
             if (lane == 0) mbar_arrive(epi_bar);
         };
-        auto epi_sync = [&]() { asm volatile("bar.sync 1, 256;" ::: "memory"); };
+        auto epi_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(CH_EPI_THREADS) : "memory"); };
         // ---- tail k-block (slot 8) of tile `tt`: per-row inputs as [hi16 | lo16 | hi16 | 0].  Done by the half-1 warps: for the first
         // tile before the loop, afterwards during the head phase of the previous tile (slot 8 is free then, the half-0 warps are
         // busy with the head epilogue), so the global loads of the next tile's inputs are off the critical path ----
@@ -349,10 +402,14 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                 store_row32(slot, row, 0, w);  // chunks 0..3: hi | lo
 #pragma unroll
                 for (int j = 0; j < 16; ++j) { w[16 + j] = 0.f; }
-                store_row32(slot, row, 4, w);  // chunks 4..7: hi | 0
+                // columns 48..53: one-hot "this row belongs to the tile's first / second object" (three each: the base MMA's A operand)
+                const int64_t rel = mm / a.rows_per_obj - ((int64_t)tt * 128) / a.rows_per_obj;
+                w[16] = w[17] = w[18] = rel == 0 ? 1.f : 0.f;
+                w[19] = w[20] = w[21] = rel == 1 ? 1.f : 0.f;
+                store_row32(slot, row, 4, w);  // chunks 4..7: hi | one-hot | 0
             }
         };
-        if (half == 1 && (int)blockIdx.x < ntiles) pack_tail((int)blockIdx.x);
+        if (part == CH_PARTS - 1 && (int)blockIdx.x < ntiles) pack_tail((int)blockIdx.x);
         arrive_epi();
         for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
             const int64_t m = (int64_t)t * 128 + row;
@@ -364,124 +421,129 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             const int64_t obj1 = obj0 + 1 < a.n_obj ? obj0 + 1 : obj0;
             const float* base_obj = a.base + obj * ldbase;
             for (int b = 0; b < a.n_blocks; ++b) {
-                // ---- stage this block's per-object base rows and sh2 in shared memory (while the fc3 MMAs run) ----
+                // ---- stage sh2 and the fc3 base tile of this block (while the fc3 MMAs run; the base MMAs are the last of the phase).
+                // Row n of a base tile = base[obj0][col0 + n] and base[obj1][col0 + n] as three bf16 parts each, K = 16 (32 bytes),
+                // 32-byte swizzle.  The previous user of the buffer (the fc1 base MMA of the previous block) completed before this
+                // warp left that block's E2. ----
+                auto write_base_tile = [&](int n, int col0) {
+                    const float v0 = __ldg(col0 < 0 ? a.sh2[b] + n : a.base + obj0 * ldbase + b * 768 + col0 + n);
+                    const float v1 = __ldg(col0 < 0 ? a.sh2[b] + n : a.base + obj1 * ldbase + b * 768 + col0 + n);
+                    uint32_t p0[3], p1[3];
+                    ch_split3(v0, p0);
+                    ch_split3(v1, p1);
+                    const int sw = (n >> 2) & 1;
+                    *reinterpret_cast<uint4*>(sBase + n * 32 + (sw << 4)) = make_uint4(p0[0] | (p0[1] << 16), p0[2] | (p1[0] << 16), p1[1] | (p1[2] << 16), 0u);
+                    *reinterpret_cast<uint4*>(sBase + n * 32 + ((sw ^ 1) << 4)) = make_uint4(0u, 0u, 0u, 0u);
+                };
+                auto arrive_base = [&]() {
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(base_bar);
+                };
                 epi_sync();  // every epilogue warp is done with the previous block's parameters
-                if (staged) {
-                    const float* g0 = a.base + obj0 * ldbase + b * 768;
-                    const float* g1 = a.base + obj1 * ldbase + b * 768;
-                    for (int i = etid; i < 768 / 4; i += 256) {
-                        reinterpret_cast<float4*>(s_base)[i] = __ldg(reinterpret_cast<const float4*>(g0) + i);
-                        reinterpret_cast<float4*>(s_base + 768)[i] = __ldg(reinterpret_cast<const float4*>(g1) + i);
-                    }
-                }
                 if (etid < 128) reinterpret_cast<float4*>(s_sh2)[etid] = __ldg(reinterpret_cast<const float4*>(a.sh2[b]) + etid);
+                if (staged) write_base_tile(etid, 256);  // fc3 columns: one of the 512 rows per epilogue thread
+                arrive_base();
                 epi_sync();
-                const float* base_b = staged ? s_base + (obj - obj0) * 768 : base_obj + b * 768;
-                // Every epilogue loop below is software-pipelined over two register buffers: the tcgen05.ld of chunk c+1 is in
-                // flight while chunk c is converted (tcgen05.wait::ld waits for ALL outstanding loads, so the next load is
-                // issued right after the wait).
-                // ---- E1: skip branch R = bf16(lrelu(fc3 + base)), packed in place into TMEM ----
-                // half 0 packs columns [0,256) upwards into [0,128); half 1 packs [256,512) DOWNWARDS into [384,512): a warp
-                // only ever overwrites columns it has already read, and [128,384) is left free as one 256-column block
+                const float* base_g = base_obj + b * 768;  // tiles over more than two objects: the base is added here, per row, from global
+                // Four warps per TMEM lane quarter, i.e. four epilogue warps per SMSP: a warp's tcgen05.ld latency is covered by the
+                // other three (plain load - wait - convert loops, 1/4 of a phase's columns each).
+                // ---- E1: skip branch R = bf16(lrelu(fc3 + base)), packed in place into TMEM: [0,256) upwards into [0,128) by parts
+                // 0 / 1, [256,512) DOWNWARDS into [384,512) by parts 2 / 3, [128,384) left free as one 256-column block.  The two warps
+                // of a pair alternate 32-column chunks (step s: chunks 2s and 2s + 1 in walking order); the packed chunk c lands in
+                // the columns of chunk c / 2, which one of the two has read in a step <= s: a 64-thread barrier between the loads and
+                // the stores of a step keeps every store behind every load it could overwrite. ----
                 wait_mma();
+                if (staged && etid < 256) write_base_tile(etid, 0);  // fc1 columns (the fc3 base MMAs are complete: the buffer is free)
+                arrive_base();
                 {
-                    uint32_t ra[32], rb[32];
-                    auto col_of = [&](int cc) { return half ? 7 - cc : cc; };
-                    auto e1 = [&](int c, const uint32_t (&r)[32]) {
-                        const float* bp = base_b + 256 + half * 256 + c * 32;
-                        uint32_t o[16];
+                    const int sub = part & 1;
+                    uint32_t ra[32];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bv = *reinterpret_cast<const float4*>(bp + 4 * j);
-                            o[2 * j] = lrelu_pack2(r[4 * j], r[4 * j + 1], bv.x, bv.y);
-                            o[2 * j + 1] = lrelu_pack2(r[4 * j + 2], r[4 * j + 3], bv.z, bv.w);
+                    for (int st = 0; st < 4; ++st) {
+                        const int cc = 2 * st + sub, c = half ? 7 - cc : cc;
+                        tmem_ld_32x32(tlane + half * 256 + c * 32, ra);
+                        tmem_ld_wait();
+                        // the fc1 MMAs only need D[128,384) to have been READ: arrive as soon as this warp's last load has landed
+                        if (st == 3) arrive_epi();
+                        asm volatile("bar.sync %0, 64;" ::"r"(2 + quarter * 2 + half) : "memory");
+                        uint32_t o[16];
+                        if (staged) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) o[j] = lrelu_cvt2(ra[2 * j], ra[2 * j + 1]);
+                        } else {
+                            const float* bp = base_g + 256 + half * 256 + c * 32;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float4 bv = *reinterpret_cast<const float4*>(bp + 4 * j);
+                                o[2 * j] = lrelu_pack2(ra[4 * j], ra[4 * j + 1], bv.x, bv.y);
+                                o[2 * j + 1] = lrelu_pack2(ra[4 * j + 2], ra[4 * j + 3], bv.z, bv.w);
+                            }
                         }
                         tmem_st_32x16(tlane + (half ? 384 : 0) + c * 16, o);
-                    };
-                    tmem_ld_32x32(tlane + half * 256 + col_of(0) * 32, ra);
-#pragma unroll
-                    for (int cc = 0; cc < 8; cc += 2) {
-                        tmem_ld_wait();
-                        tmem_ld_32x32(tlane + half * 256 + col_of(cc + 1) * 32, rb);
-                        e1(col_of(cc), ra);
-                        tmem_ld_wait();
-                        if (cc + 2 < 8) tmem_ld_32x32(tlane + half * 256 + col_of(cc + 2) * 32, ra);
-                        // The fc1 MMAs only need D[128,384) to have been READ (their operands are X and the weights) and never touch
-                        // the packed R columns: arrive as soon as this warp's last accumulator load has landed, so the hand-off and
-                        // the first MMAs run under the conversion / TMEM store of the last chunk.
-                        else arrive_epi();
-                        e1(col_of(cc + 1), rb);
                     }
                 }
                 tmem_st_wait();
-                // ---- E2: H = bf16(lrelu(fc1 + base)) -> slots 0..3 (bn1 is folded into the weights and the base) ----
+                // ---- E2: H = bf16(lrelu(fc1 + base)) -> slots 0..3 (part p owns H columns [64p, 64p + 64) = slot p) ----
                 wait_mma();
+                if (staged) write_base_tile(etid, -1);  // sh2 of both fc2 halves (the fc1 base MMA is complete: the buffer is free)
+                arrive_base();
                 {
-                    uint32_t ra[32], rb[32];
-                    auto e2 = [&](int c, const uint32_t (&r)[32]) {
-                        const float* bp = base_b + half * 128 + c * 32;
+                    uint32_t ra[32];
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        tmem_ld_32x32(tlane + 128 + part * 64 + c * 32, ra);
+                        tmem_ld_wait();
                         uint32_t o[16];
+                        if (staged) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bv = *reinterpret_cast<const float4*>(bp + 4 * j);
-                            o[2 * j] = lrelu_pack2(r[4 * j], r[4 * j + 1], bv.x, bv.y);
-                            o[2 * j + 1] = lrelu_pack2(r[4 * j + 2], r[4 * j + 3], bv.z, bv.w);
+                            for (int j = 0; j < 16; ++j) o[j] = lrelu_cvt2(ra[2 * j], ra[2 * j + 1]);
+                        } else {
+                            const float* bp = base_g + part * 64 + c * 32;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float4 bv = *reinterpret_cast<const float4*>(bp + 4 * j);
+                                o[2 * j] = lrelu_pack2(ra[4 * j], ra[4 * j + 1], bv.x, bv.y);
+                                o[2 * j + 1] = lrelu_pack2(ra[4 * j + 2], ra[4 * j + 3], bv.z, bv.w);
+                            }
                         }
-                        store_row32p(sA + (half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, o);
-                    };
-                    const uint32_t t0 = tlane + 128 + half * 128;
-                    tmem_ld_32x32(t0, ra);
-#pragma unroll
-                    for (int c = 0; c < 4; c += 2) {
-                        tmem_ld_wait();
-                        tmem_ld_32x32(t0 + (c + 1) * 32, rb);
-                        e2(c, ra);
-                        tmem_ld_wait();
-                        if (c + 2 < 4) tmem_ld_32x32(t0 + (c + 2) * 32, ra);
-                        e2(c + 1, rb);
+                        store_row32p(sA + part * CH_SLOT_BYTES, row, c * 4, o);
                     }
                 }
                 arrive_epi();
                 // ---- E3 / E4: Xout = bf16(lrelu(R + fc2 + sh2)) -> slots 4..7 (h = 0) / 0..3 (h = 1) ----
                 for (int h = 0; h < 2; ++h) {
                     wait_mma();
-                    uint32_t ra[32], rb[32], qa[16], qb[16];
-                    auto e3 = [&](int c, const uint32_t (&r)[32], const uint32_t (&rr)[16]) {
-                        const float* hp = s_sh2 + h * 256 + half * 128 + c * 32;
+                    uint32_t ra[32], qa[16];
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        tmem_ld_32x32(tlane + 128 + part * 64 + c * 32, ra);
+                        tmem_ld_32x16(tlane + (h ? 384 : 0) + part * 32 + c * 16, qa);
+                        tmem_ld_wait();
+                        // the second fc2 half reads H (slots 0..3) and only needs D[128,384) read: start it under this warp's last chunk
+                        if (h == 0 && c == 1) arrive_epi();
                         uint32_t o[16];
+                        if (staged) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 hv = *reinterpret_cast<const float4*>(hp + 4 * j);
-                            o[2 * j] = lrelu_pack3(r[4 * j], r[4 * j + 1], hv.x, hv.y, rr[2 * j]);
-                            o[2 * j + 1] = lrelu_pack3(r[4 * j + 2], r[4 * j + 3], hv.z, hv.w, rr[2 * j + 1]);
+                            for (int j = 0; j < 16; ++j) o[j] = lrelu_res2(ra[2 * j], ra[2 * j + 1], qa[j]);
+                        } else {
+                            const float* hp = s_sh2 + h * 256 + part * 64 + c * 32;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float4 hv = *reinterpret_cast<const float4*>(hp + 4 * j);
+                                o[2 * j] = lrelu_pack3(ra[4 * j], ra[4 * j + 1], hv.x, hv.y, qa[2 * j]);
+                                o[2 * j + 1] = lrelu_pack3(ra[4 * j + 2], ra[4 * j + 3], hv.z, hv.w, qa[2 * j + 1]);
+                            }
                         }
-                        store_row32p(sA + ((h ? 0 : 4) + half * 2 + (c >> 1)) * CH_SLOT_BYTES, row, (c & 1) * 4, o);
-                    };
-                    const uint32_t t0 = tlane + 128 + half * 128, q0 = tlane + (h ? 384 : 0) + half * 64;
-                    tmem_ld_32x32(t0, ra);
-                    tmem_ld_32x16(q0, qa);
-#pragma unroll
-                    for (int c = 0; c < 4; c += 2) {
-                        tmem_ld_wait();
-                        tmem_ld_32x32(t0 + (c + 1) * 32, rb);
-                        tmem_ld_32x16(q0 + (c + 1) * 16, qb);
-                        e3(c, ra, qa);
-                        tmem_ld_wait();
-                        if (c + 2 < 4) {
-                            tmem_ld_32x32(t0 + (c + 2) * 32, ra);
-                            tmem_ld_32x16(q0 + (c + 2) * 16, qa);
-                        } else if (h == 0) {
-                            arrive_epi();  // the second fc2 half reads H (slots 0..3) and only needs D[128,384) read: start it under
-                        }                  // this warp's last chunk (its stores go to slots 4..7, fenced again by the h = 1 arrive)
-                        e3(c + 1, rb, qb);
+                        store_row32p(sA + ((h ? 0 : 4) + part) * CH_SLOT_BYTES, row, c * 4, o);
                     }
                     if (h == 1) arrive_epi();
                 }
             }
-            // ---- heads (half-0 warps) | next tile's tail pack (half-1 warps) ----
-            if (half == 1 && t + (int)gridDim.x < ntiles) pack_tail(t + (int)gridDim.x);
+            // ---- heads (part-0 warps) | next tile's tail pack (last part's warps) ----
+            if (part == CH_PARTS - 1 && t + (int)gridDim.x < ntiles) pack_tail(t + (int)gridDim.x);
             wait_mma();
-            if (half == 0) {
+            if (part == 0) {
                 if (KIND == DEXGG_NET_GENERATOR) {
                     uint32_t r[32];
                     tmem_ld_32x32(tlane + 128, r);

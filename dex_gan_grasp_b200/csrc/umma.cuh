@@ -43,6 +43,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw64_kmajor(uint32_t smem_addr) {
     d |= (uint64_t)4 << 61;
     return d;
 }
+// rows of 16 bf16 (32 B) under the 32-byte swizzle (16-byte chunk index ^= (row >> 2) & 1): 8-row groups 256 B apart, layout 6 = SWIZZLE_32B
+__device__ __forceinline__ uint64_t umma_desc_sw32_kmajor(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3ffffu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(256 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)6 << 61;
+    return d;
+}
 // ---- instruction descriptor, kind::f16: D = f32, A = B = bf16, both K-major, M x N ----
 //   [4,6) c_format 1 = F32   [7,10) a_format 1 = BF16   [10,13) b_format 1 = BF16   [15] a_major 0   [16] b_major 0
 //   [17,23) N >> 3           [24,29) M >> 4
