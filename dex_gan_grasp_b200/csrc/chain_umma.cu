@@ -50,7 +50,9 @@ struct ChTile {
     const float* rowscale;  // optional per-source-row scale folded in before the bf16 rounding (BatchNorm affine)
     int ld, row0, nrows;  // rows [row0, row0 + nrows) are real, the rest of the tile is zero
     int col0;           // first source column
-    int mode;           // 0: 64 plain columns; 1: tail [hi16|hi16|lo16|0]; 2: evaluator head (row 0 = hi, row 8 = lo)
+    int mode;           // 0: 64 plain columns; 1: tail [hi16|hi16|lo16|0]; 2: score head (row 0 = hi, row 8 = lo);
+                        // 3: discriminator tail [w nt | w nt | 0] against inputs [hi nt | lo nt | one-hot | 0], nt <= 24
+    int nt;             // mode 3: tail inputs
     int tile_rows;      // 128, 32 or 16
     uint32_t pad;
     uint64_t dst_off;   // byte offset of the tile in the stream
@@ -73,6 +75,8 @@ __global__ void chain_pack_kernel(const ChTile* __restrict__ tiles, unsigned cha
                 v = t.src[(int64_t)(t.row0 + r) * t.ld + t.col0 + (c & 15)];
                 lo = c >= 32;
             }
+        } else if (t.mode == 3) {
+            if (r < t.nrows && c < 2 * t.nt) v = t.src[(int64_t)(t.row0 + r) * t.ld + t.col0 + (c % t.nt)];
         } else {
             if (r == 0 || r == 8) {
                 v = t.src[t.col0 + c];
@@ -378,6 +382,37 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
             {
                 const int64_t m = (int64_t)tt * 128 + row;
                 const int64_t mm = m < a.M ? m : a.M - 1;
+                const int64_t rel = mm / a.rows_per_obj - ((int64_t)tt * 128) / a.rows_per_obj;
+                const float ind0 = rel == 0 ? 1.f : 0.f, ind1 = rel == 1 ? 1.f : 0.f;
+                unsigned char* slot = sA + CH_TAIL_SLOT * CH_SLOT_BYTES;
+                if (KIND == DEXGG_NET_DISCRIMINATOR) {
+                    // 24 inputs (rot 9 | transl 3 | joints) as [hi 24 | lo 24 | one-hot 6 | 0]: the weights of these columns are plain bf16
+                    float v[24];
+#pragma unroll
+                    for (int j = 0; j < 24; ++j) v[j] = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 9; ++j) v[j] = fmaf(__ldg(a.tail_a + j), a.in_rot[mm * 9 + j], __ldg(a.tail_c + j));
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) v[9 + j] = fmaf(__ldg(a.tail_a + 9 + j), a.in_transl[mm * 3 + j], __ldg(a.tail_c + 9 + j));
+#pragma unroll
+                    for (int j = 0; j < 12; ++j)
+                        if (j < a.nJ) v[12 + j] = fmaf(__ldg(a.tail_a + 12 + j), a.in_joint[mm * a.nJ + j], __ldg(a.tail_c + 12 + j));
+                    float w[32];
+#pragma unroll
+                    for (int j = 0; j < 24; ++j) w[j] = __bfloat162float(__float2bfloat16_rn(v[j]));
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) w[24 + j] = v[j] - w[j];
+                    store_row32(slot, row, 0, w);  // chunks 0..3: hi 24 | lo 0..7
+                    float w2[32];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) w2[j] = v[8 + j] - w[8 + j];
+                    w2[16] = w2[17] = w2[18] = ind0;
+                    w2[19] = w2[20] = w2[21] = ind1;
+#pragma unroll
+                    for (int j = 22; j < 32; ++j) w2[j] = 0.f;
+                    store_row32(slot, row, 4, w2);  // chunks 4..7: lo 8..23 | one-hot | 0
+                    return;
+                }
                 float v[16];
 #pragma unroll
                 for (int j = 0; j < 16; ++j) v[j] = 0.f;
@@ -398,14 +433,12 @@ __global__ void __launch_bounds__(CH_THREADS, 1) chain_umma_kernel(const ChainAr
                     w[j] = hi;
                     w[16 + j] = v[j] - hi;
                 }
-                unsigned char* slot = sA + CH_TAIL_SLOT * CH_SLOT_BYTES;
                 store_row32(slot, row, 0, w);  // chunks 0..3: hi | lo
 #pragma unroll
                 for (int j = 0; j < 16; ++j) { w[16 + j] = 0.f; }
                 // columns 48..53: one-hot "this row belongs to the tile's first / second object" (three each: the base MMA's A operand)
-                const int64_t rel = mm / a.rows_per_obj - ((int64_t)tt * 128) / a.rows_per_obj;
-                w[16] = w[17] = w[18] = rel == 0 ? 1.f : 0.f;
-                w[19] = w[20] = w[21] = rel == 1 ? 1.f : 0.f;
+                w[16] = w[17] = w[18] = ind0;
+                w[19] = w[20] = w[21] = ind1;
                 store_row32(slot, row, 4, w);  // chunks 4..7: hi | one-hot | 0
             }
         };
@@ -629,8 +662,9 @@ size_t chain_stream_bytes(int kind, int n_blocks, const int* has_x) {
 static inline int ch_xcol(int i) { return i < 4 ? 256 + 64 * i : 64 * (i - 4); }
 
 int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
-    DEXGG_REQUIRE(s.tailw == 16 && (s.kind == DEXGG_NET_GENERATOR || s.kind == DEXGG_NET_EVALUATOR) && s.n_blocks <= CH_MAX_BLOCKS,
-                  "chain_pack: unsupported network for the fused kernel");
+    const bool disc = s.kind == DEXGG_NET_DISCRIMINATOR;
+    DEXGG_REQUIRE((disc ? (s.tailw == 32 && s.n_tail <= 24) : (s.tailw == 16 && (s.kind == DEXGG_NET_GENERATOR || s.kind == DEXGG_NET_EVALUATOR))) &&
+                      s.n_blocks <= CH_MAX_BLOCKS, "chain_pack: unsupported network for the fused kernel");
     std::vector<ChTile> tiles;
     uint64_t off = 0;
     auto push = [&](const float* src, int ld, int row0, int nrows, int col0, int mode, int tile_rows, const float* rowscale = nullptr,
@@ -638,6 +672,7 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
         ChTile t;
         t.rowscale = rowscale;
         t.src = src; t.ld = ld; t.row0 = row0; t.nrows = nrows; t.col0 = col0; t.mode = mode; t.tile_rows = tile_rows; t.pad = khalf;
+        t.nt = 24;
         t.dst_off = off;
         off += (uint64_t)tile_rows * (khalf ? 64 : 128);
         tiles.push_back(t);
@@ -649,7 +684,7 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
                 const bool tail = (i == nkb - 1);
                 const int col0 = tail ? (s.has_x[b] ? 512 : 0) : ch_xcol(i);
                 for (int g = 0; g < nq / 2; ++g)
-                    for (int hk = 0; hk < 2; ++hk) push(s.Wt[b], KT, row_base + g * 256, 256, col0, tail ? 1 : 0, 256, s.sc[b], 1 + hk);
+                    for (int hk = 0; hk < 2; ++hk) push(s.Wt[b], KT, row_base + g * 256, 256, col0, tail ? (disc ? 3 : 1) : 0, 256, s.sc[b], 1 + hk);
             }
         };
         first_layer(256, 4);  // fc3 rows 256..767
@@ -661,7 +696,7 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
     const int hr = ch_head_rows(s.kind);
     for (int i = 0; i < CH_HEAD_TILES; ++i) {
         if (s.kind == DEXGG_NET_GENERATOR) push(s.Wh, 512, 0, s.nh, ch_xcol(i), 0, hr);
-        else push(s.Wh, 512, 0, 1, ch_xcol(i), 2, hr);
+        else push(s.Wh, 512, 0, 1, ch_xcol(i), 2, hr);  // evaluator / discriminator: one score row as hi + lo
     }
     const int has_x[CH_MAX_BLOCKS] = {s.has_x[0], s.has_x[1], s.has_x[2]};
     DEXGG_REQUIRE(off == ch_data_bytes(s.kind, s.n_blocks, has_x) && (int)tiles.size() == ch_total_tiles(s.n_blocks, has_x),
@@ -676,9 +711,10 @@ int chain_pack(const ChainPackSrc& s, __nv_bfloat16* stream, cudaStream_t st) {
 
 int chain_forward(const ChainArgs& a, cudaStream_t st) {
     DEXGG_REQUIRE(a.M >= 1 && a.stream && a.base && a.rows_per_obj >= 1, "chain_forward: bad arguments");
-    static std::atomic<unsigned long long> attr_g{0}, attr_e{0};
+    static std::atomic<unsigned long long> attr_g{0}, attr_e{0}, attr_d{0};
     DEXGG_SMEM_OPT_IN(chain_umma_kernel<DEXGG_NET_GENERATOR>, CH_SMEM_BYTES, attr_g);
     DEXGG_SMEM_OPT_IN(chain_umma_kernel<DEXGG_NET_EVALUATOR>, CH_SMEM_BYTES, attr_e);
+    DEXGG_SMEM_OPT_IN(chain_umma_kernel<DEXGG_NET_DISCRIMINATOR>, CH_SMEM_BYTES, attr_d);
     const int64_t ntiles = (a.M + 127) / 128;
 #ifdef DEXGG_DEBUG  // timing experiments only (never in a release build): weight stream off / phase timeline of CTA 0
     { const char* e = getenv("DEXGG_CHAIN_NOSTREAM"); const_cast<ChainArgs&>(a).debug_no_stream = (e && e[0] == '1') ? 1 : 0; }
@@ -693,6 +729,9 @@ int chain_forward(const ChainArgs& a, cudaStream_t st) {
     if (a.kind == DEXGG_NET_GENERATOR) {
         DEXGG_REQUIRE(a.z && a.rot && a.transl && a.joint && a.zD >= 1 && a.zD <= 16 && a.nh <= 32 && a.nJ + 9 == a.nh, "chain_forward: bad generator arguments");
         chain_umma_kernel<DEXGG_NET_GENERATOR><<<grid, CH_THREADS, CH_SMEM_BYTES, st>>>(a);
+    } else if (a.kind == DEXGG_NET_DISCRIMINATOR) {
+        DEXGG_REQUIRE(a.in_rot && a.in_transl && a.in_joint && a.nJ >= 0 && a.nJ <= 12 && a.tail_a && a.tail_c && a.p, "chain_forward: bad discriminator arguments");
+        chain_umma_kernel<DEXGG_NET_DISCRIMINATOR><<<grid, CH_THREADS, CH_SMEM_BYTES, st>>>(a);
     } else {
         DEXGG_REQUIRE(a.kind == DEXGG_NET_EVALUATOR && a.in_rot && a.in_transl && a.tail_a && a.tail_c && a.p, "chain_forward: bad evaluator arguments");
         chain_umma_kernel<DEXGG_NET_EVALUATOR><<<grid, CH_THREADS, CH_SMEM_BYTES, st>>>(a);

@@ -358,7 +358,7 @@ int pack_net(dexgg_net* n, const float* const* P, cudaStream_t st) {
     DEXGG_LAUNCH_OK("net packing kernels");
     if (n->chain_ok) {
         ChainPackSrc cs;
-        cs.kind = n->kind; cs.n_blocks = n->n_blocks; cs.tailw = n->tailw; cs.nh = n->nh; cs.Wh = n->Wh;
+        cs.kind = n->kind; cs.n_blocks = n->n_blocks; cs.tailw = n->tailw; cs.n_tail = n->n_tail; cs.nh = n->nh; cs.Wh = n->Wh;
         for (int b = 0; b < CH_MAX_BLOCKS; ++b) {
             const bool on = b < n->n_blocks;
             cs.Wt[b] = on ? n->blk[b].Wt : nullptr; cs.KT[b] = on ? n->blk[b].KT : 0;
@@ -424,7 +424,8 @@ void carve_net(dexgg_net* n, Carver& c) {
     n->chain_stream = nullptr;
     n->chain_sc = n->chain_sh = nullptr;
     n->chain_ok = 0;
-    if (n->precision == DEXGG_PRECISION_BF16 && n->kind != DEXGG_NET_DISCRIMINATOR && n->tailw == 16) {
+    // the fused chain kernel: tails of at most 16 inputs (generator, evaluator) or the discriminator's pose + joint tail of at most 24
+    if (n->precision == DEXGG_PRECISION_BF16 && (n->kind == DEXGG_NET_DISCRIMINATOR ? (n->tailw == 32 && n->n_tail <= 24) : n->tailw == 16)) {
         int hx[CH_MAX_BLOCKS] = {0, 0, 0};
         for (int b = 0; b < n->n_blocks; ++b) hx[b] = n->blk[b].has_x;
         n->chain_stream = c.take<__nv_bfloat16>(chain_stream_bytes(n->kind, n->n_blocks, hx) / 2);
@@ -458,7 +459,7 @@ void chain_common(const dexgg_net* n, ChainArgs& a, const float* base, int64_t n
     }
     a.base = base; a.n_obj = n_obj; a.rows_per_obj = rows_per_obj; a.M = M; a.bh = n->bh;
     a.z = nullptr; a.zD = n->latentD; a.z_offset = 0.f; a.rot = a.transl = a.joint = a.rot6d = nullptr;
-    a.in_rot = a.in_transl = nullptr; a.tail_a = n->tail_a; a.tail_c = n->tail_c; a.p = nullptr;
+    a.in_rot = a.in_transl = a.in_joint = nullptr; a.tail_a = n->tail_a; a.tail_c = n->tail_c; a.p = nullptr;
     a.debug_clock = nullptr; a.debug_no_stream = 0;
 }
 
@@ -753,7 +754,7 @@ static int score_forward(const dexgg_net* net, int kind, const float* bps, int64
     if (use_chain) {
         ChainArgs a;
         chain_common(net, a, w.base, n_obj, rows_per_obj, M);
-        a.in_rot = rot; a.in_transl = transl; a.p = p;
+        a.in_rot = rot; a.in_transl = transl; a.in_joint = disc ? joint : nullptr; a.p = p;
         return chain_forward(a, st);
     }
     for (int64_t r0 = 0; r0 < M; r0 += w.mc) {

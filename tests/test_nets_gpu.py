@@ -344,6 +344,27 @@ def test_bf16_mode_many_objects_vs_fp32_mode(model, model_bf16, bps_golden):
     assert md(p16, p32) < BF16_SCORE_TOL and md(d16, d32) < BF16_SCORE_TOL
 
 
+def test_bf16_discriminator_runs_on_the_fused_chain_kernel(model, model_bf16, bps_golden):
+    """The bf16 discriminator forward (filter_grasps_discriminator's scorer, networks.py:148-159) goes through the fused whole-network
+    kernel like the generator and the evaluator: a handful of launches (projection GEMM, base finish, chain kernel) instead of one
+    per layer, ragged M (not a multiple of 128, tiles over two objects), scores within BF16_SCORE_TOL of the fp32 mode."""
+    from dex_gan_grasp_b200 import _native
+    names = list(bps_golden["names"])
+    bps = torch.from_numpy(np.concatenate([bps_golden[f"{n}/bps"] for n in names]))
+    S = 333
+    z = synth.synth_latents(7 * S, 5, seed=5)
+    rot, transl, joint, _ = model.DexGANGrasp.generator.native_forward(z, bps, 0.025, False)
+    d32 = model.DexGANGrasp.discriminator.native_forward(bps, rot, transl, joint)
+    model_bf16.DexGANGrasp.discriminator.native_forward(bps, rot, transl, joint)  # packs the weights
+    torch.cuda.synchronize()
+    n0 = _native.lib().dexgg_launch_count()
+    d16 = model_bf16.DexGANGrasp.discriminator.native_forward(bps, rot, transl, joint)
+    torch.cuda.synchronize()
+    launches = _native.lib().dexgg_launch_count() - n0
+    assert launches <= 8, launches
+    assert md(d16, d32) < BF16_SCORE_TOL
+
+
 def test_pipeline_streaming_equals_one_step_at_a_time(model):
     """GraspPipeline.run_host_pipelined (copies of neighbouring steps overlap the compute, rotating buffers) returns, step by
     step, exactly what run_host returns for the same inputs."""
