@@ -336,14 +336,40 @@ def _linear_dd(x, lin, act=False):
     return F.leaky_relu(y, LRELU_SLOPE) if act else y
 
 
+class _AllReduceSumFn(torch.autograd.Function):
+    """y = sum of x over the ranks.  Every rank differentiates its own loss through y, and the gradient of the ranks' summed loss
+    w.r.t. this rank's x is the sum of those: the backward is the same all-reduce - hence differentiable to any order (the
+    WGAN-GP penalty differentiates the discriminator's input gradient once more).  Every rank runs the same sequence of them."""
+
+    @staticmethod
+    def forward(ctx, x):
+        from . import dataparallel
+        y = x.contiguous().clone()
+        dataparallel.all_reduce_sum(y, "bn_fwd")
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        return _AllReduceSumFn.apply(g)
+
+
 def _batch_norm_dd(x, bn):
-    """Train-mode BatchNorm1d with a double backward (torch's own batch_norm: elementwise / per-column glue between the
-    dexgg GEMMs).  Single process only: the cross-rank statistics exchange of _BatchNormFn has no second derivative."""
-    if _world() > 1:
-        raise NotImplementedError("dexgg: the WGAN-GP gradient-penalty pass is single-process (no cross-rank BatchNorm "
-                                  "statistics in the twice-differentiable path)")
-    y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, True,
-                     0.1 if bn.momentum is None else float(bn.momentum), BN_EPS)
+    """Train-mode BatchNorm1d with a double backward (elementwise / per-column glue between the dexgg GEMMs).  One process:
+    torch's own batch_norm.  Data parallel: the same arithmetic from GLOBAL batch statistics (two all-reduces of per-column sums,
+    _AllReduceSumFn, so the N-rank step equals the one-process step on the concatenated batch), running statistics updated like
+    nn.BatchNorm1d (momentum, unbiased variance)."""
+    momentum = 0.1 if bn.momentum is None else float(bn.momentum)
+    if _world() == 1:
+        y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, True, momentum, BN_EPS)
+    else:
+        n_total = float(x.shape[0] * _world())
+        mean = _AllReduceSumFn.apply(x.sum(0)) / n_total
+        xc = x - mean
+        var = _AllReduceSumFn.apply((xc * xc).sum(0)) / n_total
+        y = xc * torch.rsqrt(var + BN_EPS) * bn.weight + bn.bias
+        with torch.no_grad():
+            bn.running_mean.mul_(1.0 - momentum).add_(mean.detach(), alpha=momentum)
+            bn.running_var.mul_(1.0 - momentum).add_(var.detach() * (n_total / max(n_total - 1.0, 1.0)), alpha=momentum)
     if bn.num_batches_tracked is not None:
         bn.num_batches_tracked += 1
     return y

@@ -84,6 +84,55 @@ def test_batchnorm_statistics_equal_full_batch():
         assert torch.allclose((x - mean) * invstd, y, atol=1e-5)
 
 
+def _penalty_grads(x, lin, bn):
+    """A WGAN-GP-shaped second-order quantity through the twice-differentiable BatchNorm: the input gradient of the summed scores,
+    its per-row norm penalty, differentiated w.r.t. the parameters."""
+    from dex_gan_grasp_b200 import train_ops
+    x = x.clone().requires_grad_(True)
+    s = torch.sigmoid(train_ops._batch_norm_dd(lin(x), bn).sum(1, keepdim=True))
+    gx = torch.autograd.grad(s, x, torch.ones_like(s), create_graph=True)[0]
+    penalty = ((gx.norm(2, dim=1) - 1) ** 2).mean()
+    params = [lin.weight, lin.bias, bn.weight, bn.bias]
+    return penalty.detach(), torch.autograd.grad(penalty, params)
+
+
+def _make_lin_bn():
+    torch.manual_seed(3)
+    lin = torch.nn.Linear(37, 11)
+    bn = torch.nn.BatchNorm1d(11)
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+    bn.train()
+    return lin, bn
+
+
+def _bn_dd_job(rank):
+    lin, bn = _make_lin_bn()
+    x = dp.shard({"x": _full_batch()}, rank, WORLD)["x"]
+    pen, grads = _penalty_grads(x, lin, bn)
+    grads = [g.clone() for g in grads]
+    for g in grads:  # what allreduce_gradients does with .grad: average over the ranks
+        dist.all_reduce(g)
+        g.div_(WORLD)
+    dist.all_reduce(pen)
+    return pen / WORLD, grads, bn.running_mean.clone(), bn.running_var.clone()
+
+
+def test_double_backward_batchnorm_two_ranks_equals_full_batch():
+    """train_ops._batch_norm_dd with cross-rank statistics (_AllReduceSumFn, whose backward is the same all-reduce): the penalty and
+    its parameter gradients on two ranks equal the one-process result on the concatenated batch, as do the running statistics."""
+    res = _run(_bn_dd_job)
+    lin, bn = _make_lin_bn()
+    pen, grads = _penalty_grads(_full_batch(), lin, bn)
+    for r in range(WORLD):
+        p_r, g_r, rm, rv = res[r]
+        assert torch.allclose(p_r, pen, rtol=1e-5, atol=1e-7)
+        for a_, b_ in zip(g_r, grads):
+            assert torch.allclose(a_, b_, rtol=1e-4, atol=1e-6), float((a_ - b_).abs().max())
+        assert torch.allclose(rm, bn.running_mean, atol=1e-6) and torch.allclose(rv, bn.running_var, rtol=1e-5, atol=1e-6)
+
+
 def _shard_job(rank):
     lo, hi = dp.shard_objects(1024 + 3, rank, WORLD)
     seeds = [dp.object_seed(7, o) for o in range(lo, hi)]

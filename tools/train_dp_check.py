@@ -21,10 +21,11 @@ B = int(os.environ.get("DP_BATCH", "512"))
 prec = os.environ.get("DEXGG_PRECISION", "fp32")
 graph = os.environ.get("DP_GRAPH", "0") == "1"
 combined = os.environ.get("DP_COMBINED", "0") == "1"  # GAN + evaluator update per step (TrainEngine.combined_step: two chains)
+wgan = os.environ.get("DP_WGAN", "0") == "1"          # WGAN-GP variant (is_wgan): the gradient-penalty pass with cross-rank BatchNorm statistics
 
 
 def fresh():
-    m = DexGanGrasp(dict(bench.TRAIN_CFG, gpu_ids=[local], precision=prec))
+    m = DexGanGrasp(dict(bench.TRAIN_CFG, gpu_ids=[local], precision=prec, is_wgan=wgan))
     m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(7))
     m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(7))
     if combined:
@@ -34,9 +35,13 @@ def fresh():
 
 full = synth.synth_train_batch(B, seed=11)
 z = synth.synth_latents(B, 5, seed=3)
+alphas = None
+if wgan:  # the three interpolation weights of the penalty (the reference draws them per call): fixed here, sharded like the batch
+    ga = torch.Generator().manual_seed(17)
+    alphas = [torch.randn((B,) + (1,) * (full[k].dim() - 1), generator=ga) for k in ("rot_matrix", "transl", "joint_conf")]
 ref = fresh()
 for _ in range(2 if graph else 1):
-    lg = ref.update_dexgangrasp({k: v.to(dev) for k, v in full.items()}, is_train_gen=True, Zgen=z.to(dev))
+    lg = ref.update_dexgangrasp({k: v.to(dev) for k, v in full.items()}, is_train_gen=True, Zgen=z.to(dev), alphas=alphas)
     if combined:
         lg = dict(lg, **ref.update_dexevaluator({k: v.to(dev) for k, v in full.items()}))
 torch.cuda.synchronize()
@@ -52,11 +57,11 @@ if graph:
     cap = CapturedTrainStep(dp, mine, with_evaluator=combined, is_train_gen=True, warmup=1, example_z=zmine)
     lg2 = cap(mine, z=zmine)
 else:
-    lg2 = dp.update_dexgangrasp(mine, is_train_gen=True, Zgen=zmine)
+    lg2 = dp.update_dexgangrasp(mine, is_train_gen=True, Zgen=zmine, alphas=None if alphas is None else [a[rank * n:(rank + 1) * n] for a in alphas])
     if combined:
         lg2 = dict(lg2, **dp.update_dexevaluator(mine))
 torch.cuda.synchronize()
-out = {"world": world, "batch": B, "precision": prec, "captured_graph": graph, "combined": combined,
+out = {"world": world, "batch": B, "precision": prec, "captured_graph": graph, "combined": combined, "wgan": wgan,
        "engine": dp.train_engine_name(), "collectives": dataparallel.collective_counters(), "loss_abs_diff": {}, "max_weight_diff": 0.0, "max_buffer_diff": 0.0}
 for k in lg:
     # per-rank losses are means over the local shard: average them over ranks to compare with the full-batch mean
