@@ -45,13 +45,15 @@ SWEEP = [(1024, 2048), (1, 1024), (1, 16384), (1, 100000), (8, 100000), (64, 163
          (4096, 1024), (4096, 4096), (2048, 100000)]
 for (B, N) in SWEEP:
     pts = 0.08 * torch.randn((B, N, 3), device="cuda")
-    for name, flags in [("filter", 0), ("direct", 2), ("scalar", 1)]:
+    for name, flags in [("umma", 0), ("filter", 4), ("direct", 2), ("scalar", 1)]:
+        if name in ("direct", "scalar") and os.environ.get("PROBE_FAST", "1") == "1":
+            continue
         if name == "scalar" and B * N > 3e6:
             continue
         med, mn = timeit(lambda: bps_mod.bps_encode_device(basis, pts, flags=flags, ws=ws))
         pairs = 4096.0 * B * N
         r = {"B": B, "N": N, "variant": name, "ms_median": med, "ms_min": mn, "gpairs_per_s": pairs / (med * 1e-3) / 1e9,
-             "fp32_lane_ops_per_s_executed": (3 if name == "filter" else 6) * pairs / (med * 1e-3),
+             "fp32_lane_ops_per_s_executed": (0 if name == "umma" else 3 if name == "filter" else 6) * pairs / (med * 1e-3),
              "fp32_lane_ops_per_s_direct_form": 6 * pairs / (med * 1e-3)}
         res.append(r)
         print(r, flush=True)
