@@ -455,7 +455,9 @@ class DexGanGrasp(object):
     def _engine(self, rows):
         from .train_engine import TrainEngine
         eng = getattr(self, "_train_engine", None)
-        if eng is None or eng.B != rows:
+        if eng is None or eng.B != rows or eng._closed:
+            if eng is not None:
+                eng.close()  # another batch size (a last, smaller batch of an epoch): the old engine's device buffers go first
             eng = self._train_engine = TrainEngine(self, rows)
         return eng
 

@@ -220,6 +220,7 @@ class TrainEngine:
         self.slab_ctas = 0  # 0: the library's default slab grid; combined_step sets 1 while its two chains run concurrently
         self.world = _world()
         self.rank = dist.get_rank() if self.world > 1 else 0
+        self._closed = False
         self._setup_exchange()
         self.grad_ctas = int(os.environ.get("DEXGG_GRAD_CTAS", "0"))
         self.wgrad_streams = os.environ.get("DEXGG_WGRAD_STREAMS", "1") != "0"
@@ -311,6 +312,42 @@ class TrainEngine:
         dataparallel._COUNTERS["p2p_grad_bytes"] = dataparallel._COUNTERS.get("p2p_grad_bytes", 0) + 4 * net.flat_grad.numel()
         _native.check(_L().dexgg_grad_allreduce(ctypes.byref(c), net.grad_peers.data_ptr(), net.flat_grad.numel(), 1.0 / self.world,
                                                 self.grad_ctas, _st(self.dev)))
+
+    def close(self):
+        """Release what this engine allocated outside torch's allocator: the peer-mapped exchange scratch and gradient buffers
+        (cudaMalloc + cudaIpc mappings of the other ranks').  Gradients that live in them are detached from the parameters first.
+        Every rank must close at the same point of its program (the mappings of a rank's buffer are closed by its peers)."""
+        if getattr(self, "_closed", True):
+            return
+        self._closed = True
+        L = _L()
+        with torch.cuda.device(self.dev):
+            torch.cuda.synchronize(self.dev)
+            if getattr(self, "grad_p2p", False):
+                for n in (self.G, self.D, self.E):
+                    for p_ in n.params:
+                        p_.grad = None
+                    n.module._dexgg_flat_grad = None
+                    n.flat_grad = None
+            if self.world > 1 and dist.is_initialized():
+                dist.barrier()  # nobody is still inside a kernel that writes into a peer's buffer
+            for q in getattr(self, "_peer_opened", []):
+                L.dexgg_peer_close(q)
+            self._peer_opened = []
+            if self.world > 1 and dist.is_initialized():
+                dist.barrier()  # every mapping is closed before its owner frees the allocation
+            for name in ("_grad_mine", "_peer_mine"):
+                ptr = getattr(self, name, None)
+                if ptr is not None and ptr.value:
+                    L.dexgg_peer_free(ptr)
+                    setattr(self, name, None)
+
+    def __del__(self):
+        try:
+            if self.world == 1:  # multi-rank teardown needs the collective close() call; a finaliser cannot provide it
+                self.close()
+        except Exception:
+            pass
 
     def _comm(self, a):
         c = a.comm

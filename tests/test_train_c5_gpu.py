@@ -273,3 +273,31 @@ def test_captured_step_follows_learning_rate_changes(precision):
         step.close()
     finally:
         train_ops.set_precision("fp32")
+
+
+@pytest.mark.gpu
+def test_engine_is_rebuilt_for_another_batch_size_and_after_close():
+    """The fused engine is sized for one batch: a different batch (the short last batch of an epoch) closes it - releasing the
+    buffers it allocated outside torch's allocator - and builds another; an explicit close() is followed by a fresh engine too.
+    Losses stay finite and the parameters keep moving."""
+    import torch
+    from dex_gan_grasp_b200 import synth
+    from dex_gan_grasp_b200.dexgangrasp import DexGanGrasp
+    import bench
+    m = DexGanGrasp(dict(bench.TRAIN_CFG, gpu_ids=[0], precision="bf16"))
+    m.DexGANGrasp.load_state_dict(synth.synth_gan_state_dict(7))
+    m.DexEvaluator.load_state_dict(synth.synth_eva_state_dict(7))
+    engines = []
+    for B in (256, 128, 128):
+        batch = {k: v.cuda() for k, v in synth.synth_train_batch(B, seed=B).items()}
+        w0 = m.DexEvaluator.out_success.weight.detach().clone()
+        out = m.update_dexevaluator(batch)
+        out.update(m.update_dexgangrasp(batch, is_train_gen=True))
+        torch.cuda.synchronize()
+        assert all(torch.isfinite(torch.as_tensor(float(v))) for v in out.values())
+        assert not torch.equal(w0, m.DexEvaluator.out_success.weight.detach())
+        engines.append(m._train_engine)
+        if len(engines) == 2:
+            assert engines[0]._closed and engines[0] is not engines[1]
+            engines[1].close()  # explicit: the next update builds a new one
+    assert engines[1]._closed and engines[2] is not engines[1] and not engines[2]._closed
