@@ -281,8 +281,12 @@ def test_captured_step_equals_eager_steps():
     for i in range(6):
         lc = step(batches[i], zs[i])
     torch.cuda.synchronize()
+    # Tolerances: two runs of the SAME seven steps differ by fp32 atomics noise in the BatchNorm column sums, which Adam turns into
+    # up to a full step of lr on parameters whose gradient is near zero (below); from there the generator's poses, the losses on
+    # them and the discriminator's running statistics of the fake batch drift by the same order (measured run to run, this test
+    # alone in a process, 12 runs: losses up to 1.4e-4 relative, disc_bn1.running_mean up to 7.7e-4).  Bounds are ~3x that.
     for k in le:
-        assert abs(float(le[k]) - float(lc[k])) < 1e-4 * max(1.0, abs(float(le[k]))), (k, float(le[k]), float(lc[k]))
+        assert abs(float(le[k]) - float(lc[k])) < 5e-4 * max(1.0, abs(float(le[k]))), (k, float(le[k]), float(lc[k]))
     for name in ("DexGANGrasp", "DexEvaluator"):
         sa, sb = getattr(eager, name).state_dict(), getattr(cap, name).state_dict()
         params = {k for k, _ in getattr(eager, name).named_parameters()}
@@ -295,6 +299,6 @@ def test_captured_step_equals_eager_steps():
                 d = (sa[k].double() - sb[k].double()).abs()
                 assert float(d.max()) <= 2.1e-4 * 7 and float(d.mean()) < 3e-5, (name, k, float(d.max()), float(d.mean()))
             else:
-                assert md(sa[k], sb[k]) < 2e-4 * max(1.0, float(sa[k].abs().max())), (name, k, md(sa[k], sb[k]))
+                assert md(sa[k], sb[k]) < 2.5e-3 * max(1.0, float(sa[k].abs().max())), (name, k, md(sa[k], sb[k]))
     so = cap.optim_dexgangrasp_generator.state_dict()["state"]
     assert all(int(s["step"]) == 7 for s in so.values())
