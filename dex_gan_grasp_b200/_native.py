@@ -21,6 +21,7 @@ SIGNATURES = {
     "dexgg_bps_workspace_bytes": (c_size_t, [c_int, c_int]),
     "dexgg_bps_encode_static_max_keys": (c_size_t, []),
     "dexgg_bps_encode_static": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int, c_void_p]),
+    "dexgg_center_clouds": (c_int, [c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "dexgg_bps_encode": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int,
                                  c_void_p, c_size_t, c_void_p]),
     "dexgg_bps_encode_host": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int]),

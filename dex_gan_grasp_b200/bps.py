@@ -63,6 +63,26 @@ def bps_encode_device(basis, pts, offsets=None, n_clouds=None, max_cloud_points=
     return dists, idx
 
 
+def center_clouds_device(pts, offsets=None, max_cloud_points=None, out=None):
+    """obj_pcd.translate(-obj_pcd.get_center()) (dexgangrasp_real_robot.py:133-134) on the device: pts [B,N,3] or [total,3] f32 cuda
+    (+ offsets [B+1] i64 cuda).  Returns (centred points f32, centres [B,3] f64); `out` may be `pts` itself."""
+    L = _native.lib()
+    assert pts.is_cuda and pts.dtype == torch.float32
+    pts = pts.contiguous()
+    if offsets is None:
+        assert pts.dim() == 3, "uniform clouds: pts must be [B,N,3]"
+        B, maxn = pts.shape[0], pts.shape[1]
+    else:
+        assert offsets.is_cuda and offsets.dtype == torch.int64 and max_cloud_points is not None
+        B, maxn = offsets.numel() - 1, int(max_cloud_points)
+    out = torch.empty_like(pts) if out is None else out
+    centers = torch.empty((B, 3), dtype=torch.float64, device=pts.device)
+    with torch.cuda.device(pts.device):
+        _native.check(L.dexgg_center_clouds(_native.ptr(pts), _native.ptr(offsets), B, maxn, pts.numel() // 3, _native.ptr(out),
+                                            _native.ptr(centers), _native.stream_ptr(pts.device)))
+    return out, centers
+
+
 class bps_torch:
     """Drop-in for `bps_torch.bps.bps_torch` restricted to what the reference uses: a custom basis and 'dists'
     (plus 'ids'/'deltas', which upstream also returns on request)."""

@@ -769,6 +769,57 @@ extern "C" int dexgg_bps_encode_static(const float* basis, int P, const float* p
     return dexgg_bps_encode(basis, P, pts, offsets, B, max_cloud_points, total_points, dists, idx, flags, ws, BPS_STATIC_BYTES, stream);
 }
 
+// ---- the step in front of the encoder: obj_pcd.translate(-obj_pcd.get_center()) (dexgangrasp_real_robot.py:133-134,
+// bps_encoder.py:69).  Open3D holds the points as doubles: the centre is the float64 mean, the shift is done in float64 and the
+// cloud goes back to float32 when bps_torch takes it.  One CTA per cloud sums in float64 in a fixed order (deterministic). ----
+__global__ void __launch_bounds__(256) cloud_center_kernel(const float* __restrict__ pts, const int64_t* __restrict__ offsets,
+                                                            int64_t uniform_n, double* __restrict__ centers) {
+    __shared__ double s[3][256];
+    const int b = blockIdx.x;
+    const int64_t o0 = offsets ? offsets[b] : (int64_t)b * uniform_n, o1 = offsets ? offsets[b + 1] : o0 + uniform_n;
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (int64_t i = o0 + threadIdx.x; i < o1; i += 256) {
+        ax += (double)pts[3 * i]; ay += (double)pts[3 * i + 1]; az += (double)pts[3 * i + 2];
+    }
+    s[0][threadIdx.x] = ax; s[1][threadIdx.x] = ay; s[2][threadIdx.x] = az;
+    __syncthreads();
+    for (int w = 128; w; w >>= 1) {
+        if ((int)threadIdx.x < w)
+            for (int c = 0; c < 3; ++c) s[c][threadIdx.x] += s[c][threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x < 3) centers[3 * b + threadIdx.x] = o1 > o0 ? s[threadIdx.x][0] / (double)(o1 - o0) : 0.0;
+}
+__global__ void __launch_bounds__(256) cloud_shift_kernel(const float* __restrict__ pts, const int64_t* __restrict__ offsets,
+                                                           int64_t uniform_n, const double* __restrict__ centers, float* __restrict__ out) {
+    const int b = blockIdx.y;
+    const int64_t o0 = offsets ? offsets[b] : (int64_t)b * uniform_n, o1 = offsets ? offsets[b + 1] : o0 + uniform_n;
+    const double cx = centers[3 * b], cy = centers[3 * b + 1], cz = centers[3 * b + 2];
+    for (int64_t i = o0 + (int64_t)blockIdx.x * 256 + threadIdx.x; i < o1; i += (int64_t)gridDim.x * 256) {
+        out[3 * i] = (float)((double)pts[3 * i] - cx);
+        out[3 * i + 1] = (float)((double)pts[3 * i + 1] - cy);
+        out[3 * i + 2] = (float)((double)pts[3 * i + 2] - cz);
+    }
+}
+
+extern "C" int dexgg_center_clouds(const float* pts, const int64_t* offsets, int B, int64_t max_cloud_points, int64_t total_points,
+                                   float* pts_out, double* centers, void* stream) {
+    DEXGG_ARCH_OK();
+    DEXGG_REQUIRE(B >= 0 && max_cloud_points >= 0 && total_points >= 0, "center_clouds: bad sizes");
+    if (B == 0) return DEXGG_OK;
+    DEXGG_REQUIRE(centers && (total_points == 0 || (pts && pts_out)) && B <= 65535, "center_clouds: null pointer or more than 65535 clouds");
+    if (!offsets) DEXGG_REQUIRE(total_points == (int64_t)B * max_cloud_points, "center_clouds: uniform clouds need total_points == B*max_cloud_points");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cloud_center_kernel<<<B, 256, 0, st>>>(pts, offsets, max_cloud_points, centers);
+    int gx = (int)((max_cloud_points + 2047) / 2048);
+    if (gx < 1) gx = 1;
+    if (gx > 1024) gx = 1024;
+    cloud_shift_kernel<<<dim3(gx, B), 256, 0, st>>>(pts, offsets, max_cloud_points, centers, pts_out);
+    ::dexgg::count_launches(2);
+    DEXGG_LAUNCH_OK("center_clouds kernels");
+    return DEXGG_OK;
+}
+
 extern "C" int dexgg_bps_encode_host(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
                                      float* dists, int32_t* idx, int flags) {
     DEXGG_ARCH_OK();

@@ -80,6 +80,12 @@ int dexgg_bps_encode(const float* basis, int P, const float* pts, const int64_t*
 size_t dexgg_bps_encode_static_max_keys(void);
 int dexgg_bps_encode_static(const float* basis, int P, const float* pts, const int64_t* offsets, int B,
                             int64_t max_cloud_points, int64_t total_points, float* dists, int32_t* idx, int flags, void* stream);
+/* The step in front of the encoder, on the device: obj_pcd.translate(-obj_pcd.get_center()) as the callers do it with Open3D
+ * (dexgangrasp_real_robot.py:133-134, DexGanGrasp/data/bps_encoder.py:69).  Open3D keeps points as doubles, so per cloud:
+ * centers[b] = float64 mean of the points, pts_out = float32(double(x) - centre) (pts_out may alias pts).  Same cloud layout as
+ * dexgg_bps_encode (offsets NULL = B uniform clouds).  The caller keeps `centers` to move the grasps back (transl + pc_center, :167). */
+int dexgg_center_clouds(const float* pts, const int64_t* offsets, int B, int64_t max_cloud_points, int64_t total_points,
+                        float* pts_out, double* centers, void* stream);
 /* Same call with HOST buffers (copies in, encodes, copies back, synchronises): the shape of
  * BPSEncoder.encode_pcd_with_bps (bps_encoder.py:28-55), which hands back a numpy array. offsets is a HOST array. */
 int dexgg_bps_encode_host(const float* basis, int P, const float* pts, const int64_t* offsets, int B, float* dists,
