@@ -239,7 +239,8 @@ def test_engine_combined_step_equals_sequential_calls():
                 continue
             d = (sa[k].double() - sb[k].double()).abs()
             if k in params:  # Adam turns rounding noise in a near-zero gradient into up to lr per step (tests/test_train_gpu.py)
-                assert float(d.max()) <= 2.1e-4 * 5 and float(d.mean()) < 1e-4, (name, k, float(d.max()), float(d.mean()))
+                # (the mean bound only means something on tensors with many elements: one noise-driven step of a 6-element bias moves it)
+                assert float(d.max()) <= 2.1e-4 * 5 and (d.numel() < 1024 or float(d.mean()) < 1e-4), (name, k, float(d.max()), float(d.mean()))
             else:  # BatchNorm buffers follow the (slightly different) weights of two bf16 runs with atomic summation orders
                 assert float(d.max()) < 1e-2 * max(1.0, float(sa[k].abs().max())), (name, k, float(d.max()))
     step.close()

